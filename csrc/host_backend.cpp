@@ -1,0 +1,452 @@
+// POSIX shared-memory collectives for CPU tensors.
+//
+// This image (and the GPU box) has no MPI, so host tensors — the SPMD test-suite, the
+// "Quick-Start MLP on CPU at 3 ranks" config, scalar/metadata exchange — are served by this
+// small backend instead. It provides what the reference asks of MPI for `Array`s
+// (/root/reference/src/mpi_extensions.jl:108-111 Allreduce!, :130-133 Bcast!, :152-155 Reduce!)
+// plus a barrier (src/common.jl:91) and an all-gather for handle exchange.
+//
+// Design: one shm segment per job. Header (barrier words, attach count) followed by W staging
+// slots and one result slot. A message is processed in slot-sized chunks:
+//   allreduce: copy-in -> barrier -> rank r reduces slice r over slots 0..W-1 in rank order
+//              into the result slot -> barrier -> copy-out.
+// One owner per slice + fixed rank order => bitwise-identical results on every rank (the
+// replica-consistency rule of SURVEY.md §5.1). Every wait is bounded by a timeout so a dead
+// peer surfaces as an error rather than a hang.
+#define FMPI_HOST_ONLY
+#include "../include/fmpi.h"
+
+#include <atomic>
+#include <cerrno>
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include <fcntl.h>
+#include <sched.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <time.h>
+#include <unistd.h>
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return 1;
+}
+
+constexpr uint32_t kMagic = 0x464d5049u;  // "FMPI"
+
+struct alignas(64) Header {
+  std::atomic<uint32_t> magic;
+  uint32_t world;
+  uint64_t slot_bytes;
+  alignas(64) std::atomic<uint32_t> attached;
+  alignas(64) std::atomic<uint32_t> detached;
+  alignas(64) std::atomic<uint32_t> bar_count;
+  alignas(64) std::atomic<uint32_t> bar_gen;
+  alignas(64) std::atomic<uint32_t> aborted;
+};
+
+double now_s() {
+  timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return double(ts.tv_sec) + 1e-9 * double(ts.tv_nsec);
+}
+
+// Spin a little, then yield, then sleep: ranks are usually oversubscribed on CPU test boxes.
+struct Backoff {
+  int n = 0;
+  void pause() {
+    ++n;
+    if (n < 64) {
+#if defined(__x86_64__)
+      __builtin_ia32_pause();
+#endif
+    } else if (n < 512) {
+      sched_yield();
+    } else {
+      timespec ts{0, 50000};
+      nanosleep(&ts, nullptr);
+    }
+  }
+};
+
+// bf16 / f16 <-> f32 (host arithmetic happens in float; one rounding at the end).
+inline float bf16_to_f(uint16_t h) {
+  uint32_t u = uint32_t(h) << 16;
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+}
+inline uint16_t f_to_bf16(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return uint16_t((u >> 16) | 0x40);  // quiet NaN
+  u += 0x7fffu + ((u >> 16) & 1u);                                        // RNE
+  return uint16_t(u >> 16);
+}
+inline float f16_to_f(uint16_t h) {
+  uint32_t sign = (uint32_t(h) & 0x8000u) << 16;
+  uint32_t exp = (h >> 10) & 0x1f;
+  uint32_t man = h & 0x3ffu;
+  uint32_t u;
+  if (exp == 0) {
+    if (man == 0) {
+      u = sign;
+    } else {  // subnormal
+      int e = -1;
+      do { ++e; man <<= 1; } while ((man & 0x400u) == 0);
+      u = sign | uint32_t(127 - 15 - e) << 23 | (man & 0x3ffu) << 13;
+    }
+  } else if (exp == 31) {
+    u = sign | 0x7f800000u | man << 13;
+  } else {
+    u = sign | (exp + 127 - 15) << 23 | man << 13;
+  }
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+}
+inline uint16_t f_to_f16(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  uint32_t sign = (u >> 16) & 0x8000u;
+  int32_t exp = int32_t((u >> 23) & 0xff) - 127 + 15;
+  uint32_t man = u & 0x7fffffu;
+  if (((u >> 23) & 0xff) == 0xff) return uint16_t(sign | 0x7c00u | (man ? 0x200u : 0));
+  if (exp >= 31) return uint16_t(sign | 0x7c00u);
+  if (exp <= 0) {
+    if (exp < -10) return uint16_t(sign);
+    man |= 0x800000u;
+    uint32_t shift = uint32_t(14 - exp);
+    uint32_t half = man >> shift;
+    uint32_t rem = man & ((1u << shift) - 1);
+    uint32_t mid = 1u << (shift - 1);
+    if (rem > mid || (rem == mid && (half & 1))) ++half;
+    return uint16_t(sign | half);
+  }
+  uint32_t half = uint32_t(exp) << 10 | man >> 13;
+  uint32_t rem = man & 0x1fffu;
+  if (rem > 0x1000u || (rem == 0x1000u && (half & 1))) ++half;
+  return uint16_t(sign | half);
+}
+
+template <typename T>
+inline T apply_op(T a, T b, int op) {
+  switch (op) {
+    case FMPI_SUM: return a + b;
+    case FMPI_PROD: return a * b;
+    case FMPI_MIN: return b < a ? b : a;
+    default: return a < b ? b : a;
+  }
+}
+
+// out[i] = reduce_{r=0..W-1} slot_r[i]   for i in [lo, hi)
+template <typename T>
+void reduce_native(const uint8_t* slots, size_t slot_stride, int world, uint8_t* out, size_t lo,
+                   size_t hi, int op) {
+  T* o = reinterpret_cast<T*>(out);
+  const T* s0 = reinterpret_cast<const T*>(slots);
+  for (size_t i = lo; i < hi; ++i) o[i] = s0[i];
+  for (int r = 1; r < world; ++r) {
+    const T* s = reinterpret_cast<const T*>(slots + size_t(r) * slot_stride);
+    switch (op) {
+      case FMPI_SUM: for (size_t i = lo; i < hi; ++i) o[i] = o[i] + s[i]; break;
+      case FMPI_PROD: for (size_t i = lo; i < hi; ++i) o[i] = o[i] * s[i]; break;
+      case FMPI_MIN: for (size_t i = lo; i < hi; ++i) o[i] = s[i] < o[i] ? s[i] : o[i]; break;
+      default: for (size_t i = lo; i < hi; ++i) o[i] = o[i] < s[i] ? s[i] : o[i]; break;
+    }
+  }
+}
+
+template <float (*Load)(uint16_t), uint16_t (*Store)(float)>
+void reduce_half(const uint8_t* slots, size_t slot_stride, int world, uint8_t* out, size_t lo,
+                 size_t hi, int op) {
+  uint16_t* o = reinterpret_cast<uint16_t*>(out);
+  for (size_t i = lo; i < hi; ++i) {
+    float acc = Load(reinterpret_cast<const uint16_t*>(slots)[i]);
+    for (int r = 1; r < world; ++r)
+      acc = apply_op<float>(
+          acc, Load(reinterpret_cast<const uint16_t*>(slots + size_t(r) * slot_stride)[i]), op);
+    o[i] = Store(acc);
+  }
+}
+
+size_t dtype_size(int dt) {
+  switch (dt) {
+    case FMPI_F32: case FMPI_I32: return 4;
+    case FMPI_F64: case FMPI_I64: return 8;
+    case FMPI_F16: case FMPI_BF16: case FMPI_I16: return 2;
+    case FMPI_U8: case FMPI_I8: return 1;
+    default: return 0;
+  }
+}
+
+void reduce_dispatch(int dt, const uint8_t* slots, size_t stride, int world, uint8_t* out,
+                     size_t lo, size_t hi, int op) {
+  switch (dt) {
+    case FMPI_F32: reduce_native<float>(slots, stride, world, out, lo, hi, op); break;
+    case FMPI_F64: reduce_native<double>(slots, stride, world, out, lo, hi, op); break;
+    case FMPI_I32: reduce_native<int32_t>(slots, stride, world, out, lo, hi, op); break;
+    case FMPI_I64: reduce_native<int64_t>(slots, stride, world, out, lo, hi, op); break;
+    case FMPI_I16: reduce_native<int16_t>(slots, stride, world, out, lo, hi, op); break;
+    case FMPI_U8: reduce_native<uint8_t>(slots, stride, world, out, lo, hi, op); break;
+    case FMPI_I8: reduce_native<int8_t>(slots, stride, world, out, lo, hi, op); break;
+    case FMPI_F16: reduce_half<f16_to_f, f_to_f16>(slots, stride, world, out, lo, hi, op); break;
+    case FMPI_BF16: reduce_half<bf16_to_f, f_to_bf16>(slots, stride, world, out, lo, hi, op); break;
+  }
+}
+
+}  // namespace
+
+struct fmpi_host_comm {
+  int rank = 0, world = 1;
+  size_t slot_bytes = 0;
+  double timeout_s = 300.0;
+  std::string name;
+  size_t map_bytes = 0;
+  uint8_t* base = nullptr;
+  Header* hdr = nullptr;
+  uint8_t* slots = nullptr;   // world * slot_bytes
+  uint8_t* result = nullptr;  // slot_bytes
+  uint32_t local_gen = 0;
+
+  int barrier() {
+    if (world == 1) return 0;
+    const uint32_t gen = local_gen;
+    if (hdr->bar_count.fetch_add(1, std::memory_order_acq_rel) + 1 == uint32_t(world)) {
+      hdr->bar_count.store(0, std::memory_order_relaxed);
+      hdr->bar_gen.store(gen + 1, std::memory_order_release);
+    } else {
+      Backoff b;
+      const double t0 = now_s();
+      while (hdr->bar_gen.load(std::memory_order_acquire) == gen) {
+        b.pause();
+        if ((b.n & 1023) == 0) {
+          if (hdr->aborted.load(std::memory_order_relaxed))
+            return fail("rank %d: a peer aborted the job", rank);
+          if (now_s() - t0 > timeout_s) {
+            hdr->aborted.store(1, std::memory_order_relaxed);
+            return fail("rank %d: barrier timed out after %.0f s (a peer is dead or out of step)",
+                        rank, timeout_s);
+          }
+        }
+      }
+    }
+    local_gen = gen + 1;
+    return 0;
+  }
+};
+
+extern "C" {
+
+const char* fmpi_last_error(void) { return g_err.c_str(); }
+
+int fmpi_host_init(const char* name, int rank, int world, size_t slot_bytes, double timeout_s,
+                   fmpi_host_comm** out) {
+  if (!name || !out || world < 1 || rank < 0 || rank >= world)
+    return fail("fmpi_host_init: bad arguments (rank %d, world %d)", rank, world);
+  slot_bytes = (slot_bytes + 63) & ~size_t(63);
+  if (slot_bytes == 0) slot_bytes = size_t(4) << 20;
+  auto* c = new fmpi_host_comm;
+  c->rank = rank;
+  c->world = world;
+  c->slot_bytes = slot_bytes;
+  c->timeout_s = timeout_s > 0 ? timeout_s : 300.0;
+  c->name = name;
+  const size_t hdr_bytes = (sizeof(Header) + 4095) & ~size_t(4095);
+  c->map_bytes = hdr_bytes + size_t(world + 1) * slot_bytes;
+
+  int fd = -1;
+  if (rank == 0) {
+    shm_unlink(name);  // stale segment from a crashed job with the same name
+    fd = shm_open(name, O_CREAT | O_EXCL | O_RDWR, 0600);
+    if (fd < 0) { delete c; return fail("shm_open(create %s): %s", name, strerror(errno)); }
+    if (ftruncate(fd, off_t(c->map_bytes)) != 0) {
+      const int e = errno;
+      close(fd); shm_unlink(name); delete c;
+      return fail("ftruncate: %s", strerror(e));
+    }
+  } else {
+    Backoff b;
+    const double t0 = now_s();
+    for (;;) {
+      fd = shm_open(name, O_RDWR, 0600);
+      if (fd >= 0) {
+        struct stat st;
+        if (fstat(fd, &st) == 0 && size_t(st.st_size) >= c->map_bytes) break;
+        close(fd);
+        fd = -1;
+      }
+      if (now_s() - t0 > c->timeout_s) { delete c; return fail("rank %d: timed out opening %s", rank, name); }
+      b.pause();
+    }
+  }
+  void* p = mmap(nullptr, c->map_bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+  close(fd);
+  if (p == MAP_FAILED) { const int e = errno; delete c; return fail("mmap: %s", strerror(e)); }
+  c->base = static_cast<uint8_t*>(p);
+  c->hdr = reinterpret_cast<Header*>(p);
+  c->slots = c->base + hdr_bytes;
+  c->result = c->slots + size_t(world) * slot_bytes;
+
+  if (rank == 0) {
+    c->hdr->world = uint32_t(world);
+    c->hdr->slot_bytes = slot_bytes;
+    c->hdr->attached.store(0);
+    c->hdr->detached.store(0);
+    c->hdr->bar_count.store(0);
+    c->hdr->bar_gen.store(0);
+    c->hdr->aborted.store(0);
+    c->hdr->magic.store(kMagic, std::memory_order_release);
+  } else {
+    Backoff b;
+    const double t0 = now_s();
+    while (c->hdr->magic.load(std::memory_order_acquire) != kMagic) {
+      if (now_s() - t0 > c->timeout_s) {
+        munmap(p, c->map_bytes); delete c;
+        return fail("rank %d: timed out waiting for rank 0 to initialise %s", rank, name);
+      }
+      b.pause();
+    }
+    if (c->hdr->world != uint32_t(world) || c->hdr->slot_bytes != slot_bytes) {
+      munmap(p, c->map_bytes); delete c;
+      return fail("rank %d: world/slot mismatch with rank 0", rank);
+    }
+  }
+  c->hdr->attached.fetch_add(1);
+  // Everyone attached => the name is no longer needed; unlink early so nothing leaks on crash.
+  {
+    Backoff b;
+    const double t0 = now_s();
+    while (c->hdr->attached.load(std::memory_order_acquire) < uint32_t(world)) {
+      if (now_s() - t0 > c->timeout_s) {
+        munmap(p, c->map_bytes); delete c;
+        return fail("rank %d: timed out waiting for all %d ranks to attach", rank, world);
+      }
+      b.pause();
+    }
+  }
+  if (rank == 0) shm_unlink(name);
+  *out = c;
+  return 0;
+}
+
+int fmpi_host_finalize(fmpi_host_comm* c) {
+  if (!c) return 0;
+  if (c->base) {
+    c->hdr->detached.fetch_add(1);
+    munmap(c->base, c->map_bytes);
+  }
+  delete c;
+  return 0;
+}
+
+int fmpi_host_rank(const fmpi_host_comm* c) { return c ? c->rank : -1; }
+int fmpi_host_world(const fmpi_host_comm* c) { return c ? c->world : -1; }
+
+int fmpi_host_barrier(fmpi_host_comm* c) {
+  if (!c) return fail("null communicator");
+  return c->barrier();
+}
+
+int fmpi_host_allreduce(fmpi_host_comm* c, const void* send, void* recv, size_t count, int dtype,
+                        int op) {
+  if (!c) return fail("null communicator");
+  const size_t es = dtype_size(dtype);
+  if (es == 0) return fail("unsupported dtype %d", dtype);
+  if (op < FMPI_SUM || op > FMPI_MAX) return fail("unsupported op %d", op);
+  if (c->world == 1) {
+    if (recv != send) memmove(recv, send, count * es);
+    return 0;
+  }
+  const size_t chunk = c->slot_bytes / es;
+  const uint8_t* s = static_cast<const uint8_t*>(send);
+  uint8_t* d = static_cast<uint8_t*>(recv);
+  for (size_t done = 0; done < count; done += chunk) {
+    const size_t n = count - done < chunk ? count - done : chunk;
+    memcpy(c->slots + size_t(c->rank) * c->slot_bytes, s + done * es, n * es);
+    if (c->barrier()) return 1;
+    const size_t per = (n + size_t(c->world) - 1) / size_t(c->world);
+    const size_t lo = per * size_t(c->rank) < n ? per * size_t(c->rank) : n;
+    const size_t hi = lo + per < n ? lo + per : n;
+    if (hi > lo) reduce_dispatch(dtype, c->slots, c->slot_bytes, c->world, c->result, lo, hi, op);
+    if (c->barrier()) return 1;
+    memcpy(d + done * es, c->result, n * es);
+  }
+  // The result slot must stay intact until everyone has copied it out.
+  return c->barrier();
+}
+
+int fmpi_host_reduce(fmpi_host_comm* c, const void* send, void* recv, size_t count, int dtype,
+                     int op, int root) {
+  if (!c) return fail("null communicator");
+  const size_t es = dtype_size(dtype);
+  if (es == 0) return fail("unsupported dtype %d", dtype);
+  if (op < FMPI_SUM || op > FMPI_MAX) return fail("unsupported op %d", op);
+  if (root < 0 || root >= c->world) return fail("bad root %d", root);
+  if (c->world == 1) {
+    if (recv != send) memmove(recv, send, count * es);
+    return 0;
+  }
+  const size_t chunk = c->slot_bytes / es;
+  const uint8_t* s = static_cast<const uint8_t*>(send);
+  uint8_t* d = static_cast<uint8_t*>(recv);
+  for (size_t done = 0; done < count; done += chunk) {
+    const size_t n = count - done < chunk ? count - done : chunk;
+    memcpy(c->slots + size_t(c->rank) * c->slot_bytes, s + done * es, n * es);
+    if (c->barrier()) return 1;
+    const size_t per = (n + size_t(c->world) - 1) / size_t(c->world);
+    const size_t lo = per * size_t(c->rank) < n ? per * size_t(c->rank) : n;
+    const size_t hi = lo + per < n ? lo + per : n;
+    if (hi > lo) reduce_dispatch(dtype, c->slots, c->slot_bytes, c->world, c->result, lo, hi, op);
+    if (c->barrier()) return 1;
+    if (c->rank == root) memcpy(d + done * es, c->result, n * es);
+  }
+  return c->barrier();
+}
+
+int fmpi_host_bcast(fmpi_host_comm* c, void* buf, size_t nbytes, int root) {
+  if (!c) return fail("null communicator");
+  if (root < 0 || root >= c->world) return fail("bad root %d", root);
+  if (c->world == 1) return 0;
+  uint8_t* b = static_cast<uint8_t*>(buf);
+  for (size_t done = 0; done < nbytes; done += c->slot_bytes) {
+    const size_t n = nbytes - done < c->slot_bytes ? nbytes - done : c->slot_bytes;
+    if (c->rank == root) memcpy(c->result, b + done, n);
+    if (c->barrier()) return 1;
+    if (c->rank != root) memcpy(b + done, c->result, n);
+    if (c->barrier()) return 1;
+  }
+  return 0;
+}
+
+int fmpi_host_allgather(fmpi_host_comm* c, const void* send, void* recv, size_t nbytes_each) {
+  if (!c) return fail("null communicator");
+  if (nbytes_each > c->slot_bytes)
+    return fail("allgather blob of %zu bytes exceeds the %zu-byte slot", nbytes_each, c->slot_bytes);
+  if (c->world == 1) {
+    if (recv != send) memmove(recv, send, nbytes_each);
+    return 0;
+  }
+  memcpy(c->slots + size_t(c->rank) * c->slot_bytes, send, nbytes_each);
+  if (c->barrier()) return 1;
+  uint8_t* d = static_cast<uint8_t*>(recv);
+  for (int r = 0; r < c->world; ++r)
+    memcpy(d + size_t(r) * nbytes_each, c->slots + size_t(r) * c->slot_bytes, nbytes_each);
+  return c->barrier();
+}
+
+}  // extern "C"

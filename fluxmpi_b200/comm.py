@@ -1,0 +1,280 @@
+"""Communication primitives — the reference's "MPIExtensions" layer.
+
+Reference (citations into /root/reference/src/mpi_extensions.jl):
+
+* ``allreduce!(v, op, comm)``  :97-111   → :func:`allreduce_`
+* ``bcast!(v, root, comm)``    :119-133  → :func:`bcast_`
+* ``reduce!(v, op, root, comm)`` :141-155 → :func:`reduce_` (non-root buffers untouched,
+  test/test_mpi_extensions.jl:56-60)
+* ``Iallreduce!(send, recv, op, comm)`` / ``Iallreduce!(buf, op, comm)`` :26-60 → :func:`Iallreduce`
+* ``Ibcast!(buf, root, comm)`` :70-88 → :func:`Ibcast`
+* ``cpu`` / ``gpu`` movers :5-8 → :func:`cpu`, :func:`gpu`
+
+Differences by design: device tensors are never staged through the host — they go
+to the NVLink peer-to-peer kernels of ``libfmpi_cuda.so`` (or NCCL when P2P support has been
+disabled with :func:`fluxmpi_b200.disable_p2p_support`); all calls are truly in place *and*
+return the tensor, so both calling styles of the reference work. ``comm`` is accepted and
+ignored (there is one world, like the reference's hard-coded ``MPI.COMM_WORLD``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from concurrent.futures import Future
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _native, runtime
+from ._native import op_code
+
+COMM_WORLD = "COMM_WORLD"
+
+_TORCH_DTYPES = {
+    torch.float32: _native.F32, torch.float64: _native.F64, torch.float16: _native.F16,
+    torch.bfloat16: _native.BF16, torch.int32: _native.I32, torch.int64: _native.I64,
+    torch.uint8: _native.U8, torch.int8: _native.I8, torch.int16: _native.I16,
+    torch.bool: _native.U8,
+}
+
+
+def dtype_code(dt: torch.dtype) -> int:
+    try:
+        return _TORCH_DTYPES[dt]
+    except KeyError:
+        raise TypeError(f"dtype {dt} is not supported by the collectives") from None
+
+
+# ------------------------------------------------------------------------------ movers
+
+
+def cpu(x):
+    """Move arrays to host memory; anything that is not an array passes through
+    (src/mpi_extensions.jl:5,7)."""
+    return x.cpu() if isinstance(x, torch.Tensor) else x
+
+
+def gpu(x):
+    """Move arrays to this rank's GPU; non-arrays pass through (src/mpi_extensions.jl:6,8)."""
+    if isinstance(x, torch.Tensor):
+        return x.to(runtime.current_device()) if torch.cuda.is_available() else x
+    if isinstance(x, np.ndarray) and torch.cuda.is_available():
+        return torch.from_numpy(x).to(runtime.current_device())
+    return x
+
+
+# ------------------------------------------------------------------------------ requests
+
+
+class Request:
+    """Handle of a non-blocking collective (``MPI.Request``). ``wait()`` ≙ ``MPI.Wait!``.
+
+    Host tensors: completes when the worker thread has finished the collective.
+    Device tensors: wraps a CUDA event recorded on the communication stream; ``wait()`` makes
+    the *current stream* wait for it (no host block) unless ``sync=True``.
+    """
+
+    def __init__(self, future: Optional[Future] = None, event: "torch.cuda.Event | None" = None,
+                 buffer=None):
+        self._future = future
+        self._event = event
+        self.buffer = buffer  # keeps the buffer alive, like req.buffer at mpi_extensions.jl:47
+
+    def wait(self, sync: bool = False):
+        if self._future is not None:
+            self._future.result()
+            self._future = None
+        if self._event is not None:
+            if sync:
+                self._event.synchronize()
+            else:
+                torch.cuda.current_stream().wait_event(self._event)
+            self._event = None
+        return self.buffer
+
+    def test(self) -> bool:
+        if self._future is not None and not self._future.done():
+            return False
+        if self._event is not None and not self._event.query():
+            return False
+        return True
+
+
+def Waitall(requests, sync: bool = False) -> None:
+    """``MPI.Waitall!`` (src/optimizer.jl:59)."""
+    for r in requests:
+        r.wait(sync=sync)
+
+
+# ------------------------------------------------------------------------------ helpers
+
+
+def _as_tensor(v):
+    if isinstance(v, torch.Tensor):
+        return v
+    if isinstance(v, np.ndarray):
+        return torch.from_numpy(v)
+    raise TypeError(f"collectives need a torch.Tensor or numpy array, got {type(v).__name__}")
+
+
+def _host_view(t: torch.Tensor):
+    """(contiguous work tensor, needs_copy_back)"""
+    if t.is_contiguous():
+        return t, False
+    return t.contiguous(), True
+
+
+def _host_allreduce_now(send: torch.Tensor, recv: torch.Tensor, op: int):
+    S = runtime.state()
+    if S.world == 1:
+        if recv.data_ptr() != send.data_ptr():
+            recv.copy_(send)
+        return
+    s, _ = _host_view(send)
+    r, back = _host_view(recv)
+    _native.host_check(
+        _native.host().fmpi_host_allreduce(S.host_comm, s.data_ptr(), r.data_ptr(), s.numel(),
+                                           dtype_code(s.dtype), op), "allreduce")
+    if back:
+        recv.copy_(r)
+
+
+def _host_bcast_now(buf: torch.Tensor, root: int):
+    S = runtime.state()
+    if S.world == 1:
+        return
+    b, back = _host_view(buf)
+    _native.host_check(
+        _native.host().fmpi_host_bcast(S.host_comm, b.data_ptr(), b.numel() * b.element_size(),
+                                       root), "bcast")
+    if back:
+        buf.copy_(b)
+
+
+def _host_reduce_now(send: torch.Tensor, recv: torch.Tensor, op: int, root: int):
+    S = runtime.state()
+    if S.world == 1:
+        if recv.data_ptr() != send.data_ptr():
+            recv.copy_(send)
+        return
+    s, _ = _host_view(send)
+    r, back = _host_view(recv)
+    _native.host_check(
+        _native.host().fmpi_host_reduce(S.host_comm, s.data_ptr(), r.data_ptr(), s.numel(),
+                                        dtype_code(s.dtype), op, root), "reduce")
+    if back and S.rank == root:
+        recv.copy_(r)
+
+
+def _check_pair(send: torch.Tensor, recv: torch.Tensor):
+    if send.shape != recv.shape or send.dtype != recv.dtype or send.device != recv.device:
+        raise ValueError("send and recv buffers must agree in shape, dtype and device")
+
+
+def _device_world():
+    dw = runtime.state().device_world
+    if dw is None:
+        raise RuntimeError("device collectives need Init() on a CUDA machine")
+    return dw
+
+
+# ------------------------------------------------------------------------------ blocking API
+
+
+def allreduce_(v, op="sum", comm=COMM_WORLD):
+    """In-place all-reduce of ``v`` with ``op``; returns ``v``.
+
+    CPU tensors / numpy arrays: POSIX-shm backend. CUDA tensors: NVLink P2P kernel enqueued on
+    the current stream (stream-ordered, like every torch op)."""
+    if not runtime.Initialized():
+        raise runtime.FluxMPINotInitializedError()
+    t = _as_tensor(v)
+    code = op_code(op)
+    dtype_code(t.dtype)
+    if t.is_cuda:
+        _device_world().allreduce(t, code)
+    else:
+        runtime.host_submit(_host_allreduce_now, t, t, code).result()
+    return v
+
+
+def bcast_(v, root: int = 0, comm=COMM_WORLD):
+    """In-place broadcast of ``v`` from ``root``; returns ``v``."""
+    if not runtime.Initialized():
+        raise runtime.FluxMPINotInitializedError()
+    t = _as_tensor(v)
+    _check_root(root)
+    if t.is_cuda:
+        _device_world().bcast(t, root)
+    else:
+        runtime.host_submit(_host_bcast_now, t, root).result()
+    return v
+
+
+def reduce_(v, op="sum", root: int = 0, comm=COMM_WORLD):
+    """Reduce to ``root`` in place; non-root buffers are left untouched. Returns ``v``."""
+    if not runtime.Initialized():
+        raise runtime.FluxMPINotInitializedError()
+    t = _as_tensor(v)
+    code = op_code(op)
+    _check_root(root)
+    dtype_code(t.dtype)
+    if t.is_cuda:
+        _device_world().reduce(t, code, root)
+    else:
+        runtime.host_submit(_host_reduce_now, t, t, code, root).result()
+    return v
+
+
+def barrier(comm=COMM_WORLD):
+    """Host barrier (``MPI.Barrier``)."""
+    runtime.host_barrier()
+
+
+def _check_root(root: int):
+    if not (0 <= int(root) < runtime.total_workers()):
+        raise ValueError(f"root {root} out of range for {runtime.total_workers()} workers")
+
+
+# ------------------------------------------------------------------------------ non-blocking API
+
+
+def Iallreduce(*args, comm=COMM_WORLD):
+    """``Iallreduce(send, recv, op)`` or in-place ``Iallreduce(buf, op)`` → ``(recv, request)``.
+    The values in ``recv`` are valid after ``request.wait()``."""
+    if not runtime.Initialized():
+        raise runtime.FluxMPINotInitializedError()
+    if len(args) == 3:
+        send, recv, op = args
+    elif len(args) == 2:
+        (recv, op), send = args, args[0]
+    else:
+        raise TypeError("Iallreduce(send, recv, op) or Iallreduce(buf, op)")
+    s, r = _as_tensor(send), _as_tensor(recv)
+    _check_pair(s, r)
+    code = op_code(op)
+    dtype_code(s.dtype)
+    if r.is_cuda:
+        ev = _device_world().allreduce_async(s, r, code)
+        return recv, Request(event=ev, buffer=recv)
+    fut = runtime.host_submit(_host_allreduce_now, s, r, code)
+    return recv, Request(future=fut, buffer=recv)
+
+
+def Ibcast(buf, root: int = 0, comm=COMM_WORLD):
+    """Non-blocking broadcast → ``(buf, request)``."""
+    if not runtime.Initialized():
+        raise runtime.FluxMPINotInitializedError()
+    b = _as_tensor(buf)
+    _check_root(root)
+    if b.is_cuda:
+        ev = _device_world().bcast_async(b, root)
+        return buf, Request(event=ev, buffer=buf)
+    fut = runtime.host_submit(_host_bcast_now, b, root)
+    return buf, Request(future=fut, buffer=buf)
+
+
+# Julia-style aliases so reference scripts translate 1:1 (`allreduce!` → `allreduce_b`).
+allreduce = allreduce_
+bcast = bcast_
+reduce = reduce_

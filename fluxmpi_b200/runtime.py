@@ -1,0 +1,308 @@
+"""Process runtime: Init, rank/size, rank-ordered printing, configuration.
+
+Reference behaviour being reproduced (citations into /root/reference):
+
+* ``Init(; gpu_devices, verbose)`` — src/common.jl:16-45. Idempotent, joins the job, binds a
+  device. Ours binds GPU ``LOCAL_RANK`` by default (the reference's ``(rank+1) % ndev`` puts
+  rank 0 on GPU 1) and keeps the ``gpu_devices`` override.
+* ``Initialized()`` — src/common.jl:6.
+* ``local_rank()`` / ``total_workers()`` — src/common.jl:52-69; raise
+  ``FluxMPINotInitializedError`` before Init; plain ints, hence constants under autograd
+  (the reference marks them ``@non_differentiable``).
+* ``fluxmpi_print`` / ``fluxmpi_println`` — src/common.jl:72-98: timestamp only before Init,
+  bare print at one worker, else ``"<ts> [rank / size] "`` serialised in rank order.
+* ``disable_cudampi_support`` — src/FluxMPI.jl:51-56 → ``disable_p2p_support``.
+
+Process model: SPMD, one process per GPU. Ranks come from ``RANK`` / ``WORLD_SIZE`` /
+``LOCAL_RANK`` (set by ``python -m fluxmpi_b200.launch`` or by ``torchrun``). The host world is
+our own POSIX-shm backend (no MPI on this image); the device world is a symmetric heap mapped
+into every peer (parallel/device_world.py). ``torch.distributed`` is only brought up on demand
+for the NCCL fallback / baseline.
+"""
+from __future__ import annotations
+
+import atexit
+import ctypes as C
+import datetime as _dt
+import os
+import sys
+import threading
+import warnings
+from concurrent.futures import ThreadPoolExecutor
+from dataclasses import dataclass, field
+from typing import Optional, Sequence
+
+import torch
+
+from . import _native
+from .utils import prefs
+
+
+class FluxMPINotInitializedError(RuntimeError):
+    """Raised by local_rank()/total_workers() before Init (src/FluxMPI.jl:59-63)."""
+
+    def __init__(self):
+        super().__init__("Please call fluxmpi_b200.Init(...) before using FluxMPI functionalities!")
+
+
+@dataclass
+class _State:
+    initialized: bool = False
+    rank: int = 0
+    world: int = 1
+    local_rank: int = 0
+    local_world: int = 1
+    device: Optional[torch.device] = None
+    job: str = ""
+    host_comm: Optional[int] = None           # fmpi_host_comm*
+    host_pool: Optional[ThreadPoolExecutor] = None
+    device_world: object = None               # parallel.device_world.DeviceWorld
+    p2p_disabled: bool = False
+    topology: dict = field(default_factory=dict)
+    timeout_s: float = 300.0
+    lock: threading.Lock = field(default_factory=threading.Lock)
+
+
+_S = _State()
+
+# ---------------------------------------------------------------------------- configuration
+
+if "FLUXMPI_DISABLE_CUDAMPI_SUPPORT" in os.environ:
+    # src/FluxMPI.jl:17-19 — the legacy env var only warns.
+    warnings.warn(
+        "FLUXMPI_DISABLE_CUDAMPI_SUPPORT environment variable has been removed and has no "
+        "effect. Please use `fluxmpi_b200.disable_p2p_support()` instead.", stacklevel=2)
+
+_S.p2p_disabled = bool(prefs.load_preference(prefs.KEY_DISABLE_P2P, False)) or \
+    os.environ.get("FMPI_DISABLE_P2P", "0") not in ("0", "", "false", "False")
+
+
+def disable_p2p_support(disable: bool = True):
+    """Persist the "no NVLink P2P / multicast kernels" switch. Takes effect in the next
+    process (same contract as the reference's preference, src/FluxMPI.jl:46-56)."""
+    p = prefs.set_preference(prefs.KEY_DISABLE_P2P, bool(disable))
+    print(f"[fluxmpi_b200] NVLink P2P support {'disabled' if disable else 'enabled'} in {p}. "
+          "Restart the process for this change to take effect!", file=sys.stderr)
+
+
+# Name kept for scripts written against the reference API.
+disable_cudampi_support = disable_p2p_support
+
+
+def p2p_disabled() -> bool:
+    return _S.p2p_disabled
+
+
+# ---------------------------------------------------------------------------- init
+
+
+def Initialized() -> bool:
+    return _S.initialized
+
+
+def _env_int(name: str, default: int) -> int:
+    v = os.environ.get(name)
+    return int(v) if v not in (None, "") else default
+
+
+def _job_name() -> str:
+    job = os.environ.get("FMPI_JOB_ID")
+    if job:
+        return job
+    port = os.environ.get("MASTER_PORT", "0")
+    run = os.environ.get("TORCHELASTIC_RUN_ID", "none")
+    return f"{port}-{run}-{os.getuid()}"
+
+
+def Init(gpu_devices: Optional[Sequence[int]] = None, verbose: bool = False,
+         slot_bytes: int = 8 << 20, timeout_s: Optional[float] = None,
+         device_window_bytes: Optional[int] = None) -> None:
+    """Set up the data-parallel world. Safe to call more than once."""
+    if _S.initialized:
+        if verbose:
+            fluxmpi_println("FluxMPI already initialized; Skipping...")
+        return
+    with _S.lock:
+        rank = _env_int("RANK", 0)
+        world = _env_int("WORLD_SIZE", 1)
+        lrank = _env_int("LOCAL_RANK", rank)
+        lworld = _env_int("LOCAL_WORLD_SIZE", world)
+        if not (0 <= rank < world):
+            raise ValueError(f"bad RANK={rank} for WORLD_SIZE={world}")
+        _S.rank, _S.world, _S.local_rank, _S.local_world = rank, world, lrank, lworld
+        _S.timeout_s = float(timeout_s if timeout_s is not None
+                             else os.environ.get("FMPI_TIMEOUT_S", 300.0))
+        _S.job = _job_name()
+
+        if world > 1:
+            lib = _native.host()
+            h = C.c_void_p()
+            name = ("/fmpi_" + "".join(ch if ch.isalnum() else "_" for ch in _S.job))[:200]
+            _native.host_check(
+                lib.fmpi_host_init(name.encode(), rank, world, slot_bytes, _S.timeout_s,
+                                   C.byref(h)), "fmpi_host_init")
+            _S.host_comm = h.value
+        # One worker => host collectives (blocking and non-blocking) execute in issue order.
+        _S.host_pool = ThreadPoolExecutor(max_workers=1, thread_name_prefix="fmpi-host")
+        _S.initialized = True
+
+    if verbose and world == 1:
+        warnings.warn("Using FluxMPI with only 1 worker. It might be faster to run the code "
+                      "without MPI", stacklevel=2)
+
+    if torch.cuda.is_available():
+        ndev = torch.cuda.device_count()
+        if gpu_devices is None:
+            dev = lrank % ndev
+        else:
+            dev = int(gpu_devices[rank])
+        if verbose:
+            fluxmpi_println(f"Using GPU {dev}")
+        torch.cuda.set_device(dev)
+        _S.device = torch.device("cuda", dev)
+        from .parallel import device_world
+        _S.device_world = device_world.create(
+            rank=rank, world=world, device=dev, job=_S.job, disabled=_S.p2p_disabled,
+            window_bytes=device_window_bytes, verbose=verbose)
+        _S.topology = _S.device_world.topology
+    else:
+        _S.device = torch.device("cpu")
+        if verbose:
+            fluxmpi_println("Using CPU")
+    atexit.register(Finalize)
+
+
+def Finalize() -> None:
+    """Tear the world down (the reference relies on ``MPI.Finalize``, test/test_common.jl:15)."""
+    if not _S.initialized:
+        return
+    with _S.lock:
+        if _S.device_world is not None:
+            try:
+                _S.device_world.close()
+            except Exception:
+                pass
+            _S.device_world = None
+        if _S.host_pool is not None:
+            _S.host_pool.shutdown(wait=True)
+            _S.host_pool = None
+        if _S.host_comm is not None:
+            _native.host().fmpi_host_finalize(_S.host_comm)
+            _S.host_comm = None
+        _S.initialized = False
+
+
+def local_rank() -> int:
+    if not _S.initialized:
+        raise FluxMPINotInitializedError()
+    return _S.rank
+
+
+def total_workers() -> int:
+    if not _S.initialized:
+        raise FluxMPINotInitializedError()
+    return _S.world
+
+
+def node_local_rank() -> int:
+    """Rank within the node (``LOCAL_RANK``); the reference has no such notion
+    (src/common.jl:33-34 uses the global rank)."""
+    if not _S.initialized:
+        raise FluxMPINotInitializedError()
+    return _S.local_rank
+
+
+def current_device() -> torch.device:
+    if not _S.initialized:
+        raise FluxMPINotInitializedError()
+    return _S.device
+
+
+def topology() -> dict:
+    return dict(_S.topology)
+
+
+def state() -> _State:
+    return _S
+
+
+# ---------------------------------------------------------------------------- host helpers
+
+
+def host_submit(fn, *args):
+    """Run ``fn`` on the single host-communication worker (keeps collective order)."""
+    if not _S.initialized:
+        raise FluxMPINotInitializedError()
+    return _S.host_pool.submit(fn, *args)
+
+
+def _host_barrier_now():
+    if _S.world > 1:
+        _native.host_check(_native.host().fmpi_host_barrier(_S.host_comm), "barrier")
+
+
+def host_barrier():
+    """CPU-side barrier across all ranks (``MPI.Barrier``, src/common.jl:91). Never touches a
+    GPU stream."""
+    if not _S.initialized:
+        raise FluxMPINotInitializedError()
+    if _S.world > 1:
+        host_submit(_host_barrier_now).result()
+
+
+def host_allgather_bytes(blob: bytes, size: Optional[int] = None) -> list[bytes]:
+    """All-gather one equal-sized blob per rank (handle exchange)."""
+    n = len(blob) if size is None else size
+    blob = blob.ljust(n, b"\0")
+    if _S.world == 1:
+        return [blob]
+
+    def run():
+        send = C.create_string_buffer(blob, n)
+        recv = C.create_string_buffer(n * _S.world)
+        _native.host_check(_native.host().fmpi_host_allgather(_S.host_comm, send, recv, n),
+                           "allgather")
+        raw = recv.raw
+        return [raw[i * n:(i + 1) * n] for i in range(_S.world)]
+
+    return host_submit(run).result()
+
+
+# ---------------------------------------------------------------------------- printing
+
+
+def _now() -> str:
+    return _dt.datetime.now().isoformat(timespec="milliseconds")
+
+
+def _emit(fn_end: str, prefix: str, args, kwargs):
+    file = kwargs.pop("file", sys.stdout)
+    end = kwargs.pop("end", fn_end)
+    sep = kwargs.pop("sep", "")
+    # Julia's print concatenates its arguments without a separator; keep that.
+    text = sep.join(str(a) for a in args)
+    file.write(prefix + text + end)
+    file.flush()
+
+
+def _fluxmpi_print(end: str, args, kwargs):
+    if not _S.initialized:
+        _emit(end, f"{_now()} ", args, kwargs)
+        return
+    if _S.world == 1:
+        _emit(end, "", args, kwargs)
+        return
+    for r in range(_S.world):
+        if r == _S.rank:
+            _emit(end, f"{_now()} [{_S.rank} / {_S.world}] ", args, dict(kwargs))
+        host_barrier()
+
+
+def fluxmpi_println(*args, **kwargs) -> None:
+    """Add rank and size information to the printed statement (src/common.jl:100-105)."""
+    _fluxmpi_print("\n", args, kwargs)
+
+
+def fluxmpi_print(*args, **kwargs) -> None:
+    """Like :func:`fluxmpi_println` without the trailing newline (src/common.jl:107-112)."""
+    _fluxmpi_print("", args, kwargs)

@@ -1,0 +1,228 @@
+/*
+ * fmpi.h — C ABI of the B200-native data-parallel runtime.
+ *
+ * One ABI, two consumers: the Python package (ctypes) and the Julia binding (ccall).
+ * Everything is pointer / size / enum / cudaStream_t based so torch tensors and CUDA.jl
+ * CuArrays can be handed over without copies.
+ *
+ * Two shared objects implement it:
+ *   libfmpi_host.so  (csrc/host_backend.cpp, csrc/fdx.cpp)   — no CUDA dependency; POSIX-shm
+ *                     collectives for CPU tensors + Unix-socket FD exchange.
+ *   libfmpi_cuda.so  (csrc/symm.cpp, csrc/topo.cpp, csrc/kernels/ *.cu) — sm_100a kernels,
+ *                     symmetric heap (VMM / multicast / CUDA-IPC), topology discovery.
+ *
+ * Reference parity (nikopj/FluxMPI.jl): the host collectives stand in for
+ * MPI.Allreduce!/Bcast!/Reduce! on Arrays (src/mpi_extensions.jl:108-111,130-133,152-155);
+ * the device collectives replace the CuArray methods (src/mpi_extensions.jl:97-106,119-128,
+ * 141-150) and the fused kernels replace src/optimizer.jl:20-23.
+ *
+ * All functions return 0 on success, non-zero on failure; fmpi_last_error() /
+ * fmpi_cuda_last_error() return a thread-local message for the last failure.
+ */
+#ifndef FMPI_H_
+#define FMPI_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FMPI_MAX_RANKS 8      /* one NVSwitch domain */
+#define FMPI_MAX_BLOCKS 160   /* max CTAs per rank of any cross-GPU kernel */
+#define FMPI_NUM_CHANNELS 4   /* independent signal channels (one per concurrent stream) */
+
+typedef enum {
+  FMPI_F32 = 0, FMPI_F64 = 1, FMPI_F16 = 2, FMPI_BF16 = 3,
+  FMPI_I32 = 4, FMPI_I64 = 5, FMPI_U8 = 6, FMPI_I8 = 7, FMPI_I16 = 8
+} fmpi_dtype;
+
+typedef enum { FMPI_SUM = 0, FMPI_PROD = 1, FMPI_MIN = 2, FMPI_MAX = 3 } fmpi_op;
+
+/* Optimiser rules that have a fused kernel. Semantics follow Optimisers.jl
+ * (the package the reference plugs into at src/optimizer.jl:20-25). */
+typedef enum {
+  FMPI_RULE_DESCENT = 0,   /* x -= eta*g */
+  FMPI_RULE_MOMENTUM = 1,  /* v = rho*v + eta*g ; x -= v */
+  FMPI_RULE_NESTEROV = 2,  /* d = -rho^2*v + (1+rho)*eta*g ; v = rho*v - eta*g ; x -= d */
+  FMPI_RULE_ADAM = 3,      /* m,v moments; x -= eta * mhat / (sqrt(vhat)+eps) */
+  FMPI_RULE_ADAMW = 4      /* Adam then x -= lambda*x (OptimiserChain(Adam, WeightDecay)) */
+} fmpi_rule;
+
+/* ------------------------------------------------------------------ host backend */
+
+typedef struct fmpi_host_comm fmpi_host_comm;
+
+const char* fmpi_last_error(void);
+
+/* Join (rank 0: create) the shared-memory world `name` ("/fmpi_<job>"); slot_bytes is the
+ * per-rank staging size (messages larger than that are chunked). timeout_s bounds every wait
+ * so a dead peer turns into an error instead of a hang. */
+int fmpi_host_init(const char* name, int rank, int world, size_t slot_bytes, double timeout_s,
+                   fmpi_host_comm** out);
+int fmpi_host_finalize(fmpi_host_comm* c);
+int fmpi_host_rank(const fmpi_host_comm* c);
+int fmpi_host_world(const fmpi_host_comm* c);
+int fmpi_host_barrier(fmpi_host_comm* c);
+/* recv may alias send (in-place). Result is bitwise identical on every rank (one owner per
+ * slice reduces in rank order 0..W-1). */
+int fmpi_host_allreduce(fmpi_host_comm* c, const void* send, void* recv, size_t count,
+                        int dtype, int op);
+int fmpi_host_bcast(fmpi_host_comm* c, void* buf, size_t nbytes, int root);
+/* Only root's recv is written; non-root buffers are left untouched
+ * (test/test_mpi_extensions.jl:56-60). */
+int fmpi_host_reduce(fmpi_host_comm* c, const void* send, void* recv, size_t count, int dtype,
+                     int op, int root);
+/* all-gather of equal-sized blobs (handle exchange, print ordering, tests) */
+int fmpi_host_allgather(fmpi_host_comm* c, const void* send, void* recv, size_t nbytes_each);
+
+/* Unix-domain-socket file-descriptor exchange (SCM_RIGHTS), used to pass CUDA VMM
+ * shareable handles between the ranks of one node. */
+int fmpi_fdx_open(const char* job, int rank, int* sock_out);
+/* Send `fd` to every peer and receive theirs: fds_out[r] for r != rank (fds_out[rank] = fd).
+ * All ranks must have returned from fmpi_fdx_open before anyone calls this. */
+int fmpi_fdx_exchange(int sock, const char* job, int rank, int world, int fd, int* fds_out,
+                      double timeout_s);
+/* Root sends one fd to everybody else (multicast object handle). */
+int fmpi_fdx_bcast(int sock, const char* job, int rank, int world, int root, int* fd_inout,
+                   double timeout_s);
+int fmpi_fdx_close(int sock, const char* job, int rank);
+const char* fmpi_fdx_last_error(void);
+
+/* ------------------------------------------------------------------ device side */
+#ifndef FMPI_HOST_ONLY
+
+typedef void* fmpi_stream; /* cudaStream_t */
+
+const char* fmpi_cuda_last_error(void);
+
+/* ---- topology (csrc/topo.cpp); replaces the reference's blind (rank+1)%ndev device pick
+ * (src/common.jl:33-34) with discovery. Writes a JSON document into buf. */
+int fmpi_topo_json(char* buf, size_t buflen);
+int fmpi_device_count(void);
+
+/* ---- symmetric heap (csrc/symm.cpp) */
+typedef struct fmpi_symm fmpi_symm;
+enum { FMPI_SYMM_VMM = 0, FMPI_SYMM_IPC = 1, FMPI_SYMM_LOCAL = 2 };
+
+/* Allocate `bytes` (rounded up to the allocation / multicast granularity) on `device`.
+ * mode VMM: cuMemCreate with a POSIX-fd shareable handle; IPC: cudaMalloc + cudaIpc handle;
+ * LOCAL: plain cudaMalloc, no sharing (world 1 and single-GPU emulation). */
+int fmpi_symm_create(int device, size_t bytes, int mode, int want_multicast, int world,
+                     fmpi_symm** out);
+size_t fmpi_symm_size(const fmpi_symm* s);
+void* fmpi_symm_local_ptr(const fmpi_symm* s);
+int fmpi_symm_mode(const fmpi_symm* s);
+/* VMM: the fd to pass to peers. */
+int fmpi_symm_export_fd(fmpi_symm* s, int* fd_out);
+/* IPC: 64-byte cudaIpcMemHandle_t. */
+int fmpi_symm_export_ipc(fmpi_symm* s, void* handle64);
+/* Map peer `r`'s allocation; afterwards fmpi_symm_peer_ptr(s, r) is valid. */
+int fmpi_symm_import_fd(fmpi_symm* s, int r, int fd);
+int fmpi_symm_import_ipc(fmpi_symm* s, int r, const void* handle64);
+int fmpi_symm_set_self(fmpi_symm* s, int rank);
+void* fmpi_symm_peer_ptr(const fmpi_symm* s, int r);
+/* Multicast (NVLS): root creates + exports, everyone imports/adds its device, then (after a
+ * host barrier) binds its memory and maps the multicast VA. */
+int fmpi_symm_mc_supported(int device);
+int fmpi_symm_mc_create(fmpi_symm* s, int* fd_out);          /* root only */
+int fmpi_symm_mc_import(fmpi_symm* s, int fd);               /* non-root */
+int fmpi_symm_mc_add_device(fmpi_symm* s);                   /* all, then barrier */
+int fmpi_symm_mc_bind_map(fmpi_symm* s);                     /* all, then barrier */
+void* fmpi_symm_mc_ptr(const fmpi_symm* s);
+int fmpi_symm_destroy(fmpi_symm* s);
+
+/* ---- device communicator: peer pointer tables handed to every kernel by value */
+typedef struct {
+  int32_t rank;           /* this process's rank (ignored when emulate != 0) */
+  int32_t world;
+  int32_t emulate;        /* != 0: single-GPU emulation, rank = blockIdx.y (cooperative launch) */
+  int32_t channel;        /* signal channel in [0, FMPI_NUM_CHANNELS) */
+  void* data[FMPI_MAX_RANKS];      /* symmetric data windows (same layout on every rank) */
+  uint32_t* sig[FMPI_MAX_RANKS];   /* symmetric signal pads (fmpi_sigpad_bytes() each) */
+  void* mc_data;          /* multicast alias of the data window, or NULL */
+  uint64_t data_bytes;    /* size of each data window */
+} fmpi_devcomm;
+
+size_t fmpi_sigpad_bytes(void);
+
+/* Launch-shape hints; 0 = library default chosen from message size. */
+typedef struct { int32_t blocks; int32_t threads; int32_t algo; } fmpi_launch;
+enum { FMPI_ALGO_AUTO = 0, FMPI_ALGO_ONESHOT = 1, FMPI_ALGO_TWOSHOT = 2, FMPI_ALGO_NVLS = 3 };
+
+/* Collectives on buffers that already live in the symmetric window at byte offset `off`
+ * (in-place, result in every rank's window for allreduce/bcast, root only for reduce). */
+int fmpi_allreduce_symm(const fmpi_devcomm* c, uint64_t off, uint64_t count, int dtype, int op,
+                        const fmpi_launch* l, fmpi_stream st);
+int fmpi_bcast_symm(const fmpi_devcomm* c, uint64_t off, uint64_t nbytes, int root,
+                    const fmpi_launch* l, fmpi_stream st);
+int fmpi_reduce_symm(const fmpi_devcomm* c, uint64_t off, uint64_t count, int dtype, int op,
+                     int root, const fmpi_launch* l, fmpi_stream st);
+
+/* Collectives on arbitrary device buffers: the kernel itself stages through the symmetric
+ * window at `stage_off` (push mode: writes go straight into the peers' slots, so there is no
+ * separate copy-in). in/out are per-emulated-rank arrays; real mode uses entry [0].
+ * stage_bytes is the size of the staging area available at stage_off. */
+int fmpi_allreduce_any(const fmpi_devcomm* c, const void* const* in, void* const* out,
+                       uint64_t count, int dtype, int op, uint64_t stage_off,
+                       uint64_t stage_bytes, const fmpi_launch* l, fmpi_stream st);
+int fmpi_bcast_any(const fmpi_devcomm* c, void* const* buf, uint64_t nbytes, int root,
+                   uint64_t stage_off, uint64_t stage_bytes, const fmpi_launch* l,
+                   fmpi_stream st);
+int fmpi_reduce_any(const fmpi_devcomm* c, const void* const* in, void* const* out,
+                    uint64_t count, int dtype, int op, int root, uint64_t stage_off,
+                    uint64_t stage_bytes, const fmpi_launch* l, fmpi_stream st);
+int fmpi_barrier_dev(const fmpi_devcomm* c, fmpi_stream st);
+
+/* ---- fused gradient allreduce (+) optimiser step (the headline kernel).
+ * Gradients (dtype gdt) at g_off and parameters (dtype pdt) at p_off live in the symmetric
+ * window; the element range [lo, hi) is one bucket. Each rank owns a 1/W slice of the bucket:
+ * it reduces that slice across all ranks (rank-ordered fp32 sum, or multimem.ld_reduce),
+ * applies the rule in registers and writes the new parameters into EVERY rank's window, so
+ * replicas stay bit-identical. Moments m, v (fp32) and the optional fp32 master copy are
+ * process-local arrays indexed like the window (only the owned slice is touched).
+ * step_dev points at a device int64 holding the number of completed steps (read only; advance
+ * it with fmpi_step_advance so CUDA-graph replays see fresh bias corrections). */
+typedef struct {
+  int32_t rule;          /* fmpi_rule */
+  float eta, beta1, beta2, eps, lambda, rho;
+  float grad_scale;      /* multiplies the summed gradient (1 = reference SUM semantics) */
+  int32_t zero_grad;     /* != 0: owner clears every rank's gradient slice after reading it */
+} fmpi_hyper;
+
+int fmpi_fused_step(const fmpi_devcomm* c, uint64_t g_off, int gdt, uint64_t p_off, int pdt,
+                    float* const* m, float* const* v, float* const* master,
+                    uint64_t lo, uint64_t hi, const fmpi_hyper* h, const int64_t* const* step_dev,
+                    const fmpi_launch* l, fmpi_stream st);
+int fmpi_step_advance(int64_t* step_dev, fmpi_stream st);
+
+/* Same rule math with no communication, over a table of scattered tensors (functional
+ * `update` on arbitrary trees). Pointer tables are device arrays of n entries. */
+int fmpi_multi_tensor_step(int n, void* const* p, const void* const* g, float* const* m,
+                           float* const* v, const uint64_t* numel, int pdt, int gdt,
+                           const fmpi_hyper* h, int64_t step, fmpi_stream st);
+
+/* ---- pack / unpack scattered leaves into / out of a flat buffer (pointer-table kernels) */
+int fmpi_pack(int n, const void* const* src, const uint64_t* offsets_bytes,
+              const uint64_t* nbytes, void* flat, fmpi_stream st);
+int fmpi_unpack(int n, void* const* dst, const uint64_t* offsets_bytes, const uint64_t* nbytes,
+                const void* flat, fmpi_stream st);
+
+/* ---- diagnostics: sum of squares (gradient norm) and a 64-bit order-independent checksum
+ * (bitwise replica-consistency checks). scratch: device buffer of fmpi_reduce_scratch_bytes()
+ * that the caller allocates once; out: device double / uint64. */
+size_t fmpi_reduce_scratch_bytes(void);
+int fmpi_sumsq(const void* x, uint64_t count, int dtype, double* out, void* scratch,
+               fmpi_stream st);
+int fmpi_checksum(const void* x, uint64_t nbytes, uint64_t* out, void* scratch, fmpi_stream st);
+
+/* Write > L2-size bytes (bench hygiene: flush L2 between timed iterations). */
+int fmpi_flush_l2(void* buf, uint64_t nbytes, fmpi_stream st);
+
+#endif /* FMPI_HOST_ONLY */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FMPI_H_ */

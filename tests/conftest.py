@@ -1,0 +1,44 @@
+"""Test harness.
+
+The reference's tests are SPMD scripts launched N-way by ``mpiexec``
+(/root/reference/test/runtests.jl:11-16); the assertions run inside every rank. Same design
+here: ``tests/spmd/*.py`` are rank scripts, ``run_spmd`` launches them with our launcher and
+asserts exit code 0. GPU tests carry ``@pytest.mark.gpu``.
+"""
+import os
+import sys
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run with -m gpu on a B200)")
+    from fluxmpi_b200 import _build
+    _build.build_host()
+
+
+def run_spmd(script: str, nprocs: int, timeout: float = 180.0, env=None, args=()):
+    from fluxmpi_b200.launch import launch
+    env_extra = {"PYTHONPATH": str(ROOT) + os.pathsep + os.environ.get("PYTHONPATH", ""),
+                 "FMPI_TIMEOUT_S": "60"}
+    if env:
+        env_extra.update(env)
+    code, outs = launch(nprocs, [str(ROOT / "tests" / "spmd" / script), *args], timeout=timeout,
+                        env_extra=env_extra, capture=True)
+    return code, outs
+
+
+@pytest.fixture
+def spmd():
+    def _run(script, nprocs, **kw):
+        code, outs = run_spmd(script, nprocs, **kw)
+        if code != 0:
+            joined = "\n".join(f"--- rank {i} ---\n{o}" for i, o in enumerate(outs))
+            pytest.fail(f"{script} at W={nprocs} exited {code}\n{joined}")
+        return outs
+    return _run

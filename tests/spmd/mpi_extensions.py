@@ -1,0 +1,109 @@
+# mirrors /root/reference/test/test_mpi_extensions.jl:1-64 (+ dtype/op/size matrix)
+import numpy as np
+import torch
+import fluxmpi_b200 as fm
+
+fm.Init(verbose=True, slot_bytes=1 << 16)   # small slots so big messages exercise chunking
+r, w = fm.local_rank(), fm.total_workers()
+
+# --- Iallreduce (test_mpi_extensions.jl:9-23)
+x = torch.ones(4, dtype=torch.float64)
+y = torch.zeros(4, dtype=torch.float64)
+y_, req = fm.Iallreduce(x, y, "+")
+req.wait()
+assert y_ is y and torch.equal(y, x * w)
+y2 = torch.zeros(4, dtype=torch.float64)
+_, req = fm.Iallreduce(x, y2, "*")
+req.wait()
+assert torch.equal(y2, x)
+# in-place form
+z = torch.full((5,), float(r + 1))
+_, req = fm.Iallreduce(z, "sum")
+fm.Waitall([req])
+assert torch.equal(z, torch.full((5,), w * (w + 1) / 2))
+
+# --- Ibcast (test_mpi_extensions.jl:25-32)
+b = torch.ones(2, 3) if r == 0 else torch.zeros(2, 3)
+b_, req = fm.Ibcast(b, 0)
+req.wait()
+assert b_ is b and torch.equal(b, torch.ones(2, 3))
+
+# --- blocking wrappers (test_mpi_extensions.jl:34-62)
+x = torch.ones(4, dtype=torch.float64)
+assert torch.equal(fm.allreduce_(x.clone(), "+"), x * w)
+assert torch.equal(fm.allreduce_(x.clone(), "*"), x)
+b = torch.ones(2, 3) if r == 0 else torch.zeros(2, 3)
+assert torch.equal(fm.bcast_(b, 0), torch.ones(2, 3))
+x = torch.ones(4, dtype=torch.float64)
+y = fm.reduce_(x.clone(), "+", 0)
+if r == 0:
+    assert torch.equal(y, x * w)
+else:
+    assert torch.equal(y, x)           # non-root unchanged (test_mpi_extensions.jl:56-60)
+
+# --- beyond the reference: every dtype x op, odd sizes, chunking, bitwise replica equality
+import operator
+gen = torch.Generator().manual_seed(1234 + r)
+for dt in (torch.float32, torch.float64, torch.float16, torch.bfloat16, torch.int32,
+           torch.int64, torch.uint8, torch.int8, torch.int16):
+    for n in (1, 7, 1000, 70001):
+        if dt.is_floating_point:
+            mine = (torch.rand(n, generator=gen, dtype=torch.float64) + 0.5).to(dt)
+        else:
+            mine = torch.randint(1, 3, (n,), generator=gen).to(dt)
+        gathered = [None] * w
+        allv = torch.zeros(w, n, dtype=dt)
+        allv[r] = mine
+        fm.allreduce_(allv, "sum")       # all-gather via sum of one-hot rows
+        for op, ref in (("sum", lambda a: a.double().sum(0)), ("prod", lambda a: a.double().prod(0)),
+                        ("min", lambda a: a.double().amin(0)), ("max", lambda a: a.double().amax(0))):
+            if op == "prod" and n > 1000:
+                continue
+            out = fm.allreduce_(mine.clone(), op)
+            want = ref(allv)
+            if dt in (torch.uint8, torch.int8, torch.int16):
+                want = want.to(torch.int64).to(dt).double()   # wrap-around like the C types
+            tol = {torch.float16: 2e-2, torch.bfloat16: 1e-1, torch.float32: 1e-5}.get(dt, 1e-12)
+            assert torch.allclose(out.double(), want, rtol=tol, atol=tol), (dt, n, op)
+            # replicas must agree bit for bit
+            chk = torch.zeros(w, n, dtype=dt)
+            chk[r] = out
+            fm.allreduce_(chk, "max")
+            assert all(torch.equal(chk[q], out) for q in range(w)), (dt, n, op, "replica drift")
+
+# bcast from every root, reduce to every root, big payload
+for root in range(w):
+    t = torch.full((33333,), float(r))
+    fm.bcast_(t, root)
+    assert torch.equal(t, torch.full((33333,), float(root)))
+    t = torch.full((12345,), 1.0 + r)
+    fm.reduce_(t, "max", root)
+    assert torch.equal(t, torch.full((12345,), float(w) if r == root else 1.0 + r))
+
+# non-contiguous tensors and numpy arrays go through the same calls
+m = torch.arange(12, dtype=torch.float32).reshape(3, 4).t()
+assert not m.is_contiguous()
+want = m.clone() * w
+fm.allreduce_(m, operator.add)
+assert torch.equal(m, want)
+a = np.full(6, r + 1.0)
+fm.allreduce_(a, "+")
+assert np.array_equal(a, np.full(6, w * (w + 1) / 2))
+
+# errors
+for bad in ("xor", 17):
+    try:
+        fm.allreduce_(torch.ones(1), bad)
+    except ValueError:
+        pass
+    else:
+        raise AssertionError("bad op accepted")
+try:
+    fm.bcast_(torch.ones(1), w)
+except ValueError:
+    pass
+else:
+    raise AssertionError("bad root accepted")
+
+fm.Finalize()
+print("RANK_OK", r)

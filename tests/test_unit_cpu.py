@@ -1,0 +1,210 @@
+"""Single-process unit tests (no launch): tree walk, rules vs torch.optim oracles, FlatParams,
+preferences, data sharding arithmetic."""
+import math
+import os
+from collections import OrderedDict, namedtuple
+
+import numpy as np
+import pytest
+import torch
+
+import fluxmpi_b200 as fm
+from fluxmpi_b200 import rules as R
+from fluxmpi_b200 import tree as T
+from fluxmpi_b200.utils import prefs
+
+
+# ------------------------------------------------------------------------------ tree
+def test_fmap_structure_and_identity_cache():
+    NT = namedtuple("NT", ["x", "y"])
+    shared = torch.ones(2)
+    tr = {"a": NT(x=shared, y=[torch.zeros(1), None, "s"]), "b": (shared, 3), "c": OrderedDict(z=1.5)}
+    calls = []
+
+    def f(v):
+        calls.append(v)
+        return v * 2 if isinstance(v, torch.Tensor) else v
+
+    out = T.fmap(f, tr)
+    assert isinstance(out["a"], NT) and isinstance(out["c"], OrderedDict)
+    assert out["a"].x is out["b"][0]                      # tied stays tied
+    assert sum(1 for c in calls if c is shared) == 1      # visited once (Functors cache)
+    assert out["a"].y[1] is None and out["a"].y[2] == "s" and out["b"][1] == 3
+    assert torch.equal(out["a"].x, torch.full((2,), 2.0))
+    assert T.fmap(f, ()) == () and T.fmap(f, {}) == {}
+
+
+def test_leaves_and_tree_equal():
+    a = {"p": torch.ones(2), "q": (np.arange(3), 2)}
+    b = {"p": torch.ones(2), "q": (np.arange(3), 2)}
+    assert T.tree_equal(a, b)
+    b["q"] = (np.arange(3), 3)
+    assert not T.tree_equal(a, b)
+    assert len(T.leaves(a)) == 3
+    assert [p for p, _ in T.leaves_with_path(a)] == [("p",), ("q", 0), ("q", 1)]
+
+
+# ------------------------------------------------------------------------------ rules
+def _run_rule(rule, steps, x0, grads):
+    ps = {"w": x0.clone()}
+    st = R.setup(rule, ps)
+    for g in grads[:steps]:
+        st, ps = R.update(st, ps, {"w": g})
+    return ps["w"]
+
+
+def _run_torch(opt_cls, kwargs, steps, x0, grads):
+    p = torch.nn.Parameter(x0.clone())
+    opt = opt_cls([p], **kwargs)
+    for g in grads[:steps]:
+        p.grad = g.clone()
+        opt.step()
+    return p.detach()
+
+
+@pytest.fixture
+def problem():
+    g = torch.Generator().manual_seed(0)
+    x0 = torch.randn(64, generator=g, dtype=torch.float64)
+    grads = [torch.randn(64, generator=g, dtype=torch.float64) for _ in range(6)]
+    return x0, grads
+
+
+def test_adam_matches_torch(problem):
+    x0, grads = problem
+    ours = _run_rule(R.Adam(1e-2, (0.9, 0.999), 1e-8), 6, x0, grads)
+    ref = _run_torch(torch.optim.Adam, dict(lr=1e-2, betas=(0.9, 0.999), eps=1e-8), 6, x0, grads)
+    assert torch.allclose(ours, ref, rtol=1e-10, atol=1e-12)
+
+
+def test_adamw_matches_torch_with_gamma_lr_wd(problem):
+    x0, grads = problem
+    lr, wd = 1e-2, 0.1
+    ours = _run_rule(R.AdamW(lr, (0.9, 0.999), lr * wd, 1e-8), 5, x0, grads)
+    ref = _run_torch(torch.optim.AdamW, dict(lr=lr, weight_decay=wd, eps=1e-8), 5, x0, grads)
+    assert torch.allclose(ours, ref, rtol=1e-9, atol=1e-11)
+
+
+def test_descent_and_momentum_match_torch(problem):
+    x0, grads = problem
+    assert torch.allclose(_run_rule(R.Descent(0.1), 4, x0, grads),
+                          _run_torch(torch.optim.SGD, dict(lr=0.1), 4, x0, grads))
+    # Optimisers' Momentum folds eta into the velocity: v = rho*v + eta*g ; x -= v.
+    # torch: buf = rho*buf + g ; x -= lr*buf  — identical trajectories for constant lr.
+    assert torch.allclose(_run_rule(R.Momentum(0.05, 0.9), 5, x0, grads),
+                          _run_torch(torch.optim.SGD, dict(lr=0.05, momentum=0.9), 5, x0, grads),
+                          rtol=1e-10, atol=1e-12)
+    assert torch.allclose(_run_rule(R.Nesterov(0.05, 0.9), 5, x0, grads),
+                          _run_torch(torch.optim.SGD, dict(lr=0.05, momentum=0.9, nesterov=True),
+                                     5, x0, grads), rtol=1e-10, atol=1e-12)
+
+
+def test_other_rules_match_torch(problem):
+    x0, grads = problem
+    assert torch.allclose(_run_rule(R.AdaMax(2e-3), 5, x0, grads),
+                          _run_torch(torch.optim.Adamax, dict(lr=2e-3, eps=1e-8), 5, x0, grads),
+                          rtol=1e-6, atol=1e-8)
+    # RMSProp: same recurrence as torch (alpha=rho, eps outside sqrt)
+    assert torch.allclose(_run_rule(R.RMSProp(1e-3, 0.9, 1e-8), 5, x0, grads),
+                          _run_torch(torch.optim.RMSprop, dict(lr=1e-3, alpha=0.9, eps=1e-8),
+                                     5, x0, grads), rtol=1e-9, atol=1e-11)
+
+
+def test_every_rule_steps_and_keeps_shapes(problem):
+    x0, grads = problem
+    for rule in (R.AdaGrad(), R.AdaDelta(), R.AMSGrad(), R.NAdam(), R.AdaBelief(), R.WeightDecay(),
+                 R.ClipGrad(0.5), R.ClipNorm(1.0), R.OptimiserChain(R.ClipNorm(1.0), R.Adam(1e-3))):
+        out = _run_rule(rule, 3, x0, grads)
+        assert out.shape == x0.shape and torch.isfinite(out).all() and not torch.equal(out, x0)
+
+
+def test_setup_tied_and_nontrainable_leaves():
+    w = torch.ones(3)
+    ps = {"a": w, "b": {"tied": w, "idx": torch.arange(3), "n": 5, "none": None}}
+    st = R.setup(R.Adam(), ps)
+    assert st["a"] is st["b"]["tied"]
+    assert st["b"]["idx"] is None and st["b"]["n"] is None and st["b"]["none"] is None
+    st2, ps2 = R.update(st, ps, {"a": torch.ones(3), "b": {"tied": torch.ones(3), "idx": None,
+                                                           "n": None, "none": None}})
+    assert ps2["a"] is ps2["b"]["tied"]               # stepped once, still tied
+    assert ps2["b"]["n"] == 5
+
+
+def test_update_inplace_mutates_and_adjust():
+    ps = {"w": torch.ones(4)}
+    st = R.setup(R.Descent(0.5), ps)
+    st, ps2 = R.update_(st, ps, {"w": torch.ones(4)})
+    assert ps2["w"] is ps["w"] and torch.equal(ps["w"], torch.full((4,), 0.5))
+    st = R.adjust(st, 0.25)
+    assert st["w"].rule.eta == 0.25
+    st = R.adjust(R.setup(fm.DistributedOptimizer(R.Adam(1e-3)), ps), 1e-2)
+    assert st["w"].rule.optimizer.eta == 1e-2
+
+
+def test_distributed_optimizer_state_equals_inner_rule():
+    """test/test_optimizer.jl:13-14 — without any world."""
+    ps = {"a": torch.zeros(4), "b": torch.zeros(4)}
+    s1 = R.setup(R.Adam(0.001), ps)
+    s2 = R.setup(fm.DistributedOptimizer(R.Adam(0.001)), ps)
+    assert T.tree_equal(s1["a"].state, s2["a"].state) and T.tree_equal(s1["b"].state, s2["b"].state)
+
+
+# ------------------------------------------------------------------------------ FlatParams
+def test_flatparams_views_and_roundtrip():
+    NT = namedtuple("NT", ["u", "v"])
+    tree = {"a": NT(u=torch.arange(6.).reshape(2, 3), v=torch.ones(2)), "b": [torch.zeros(1)], "meta": "x"}
+    fp = fm.FlatParams.from_tree(tree)
+    assert len(fp) == 9 and fp.getdata().shape == (9,)
+    assert torch.equal(fp.a.u, tree["a"].u) and fp.a.u.data_ptr() == fp.data.data_ptr()
+    fp.a.v.fill_(7)
+    assert torch.equal(fp.data[6:8], torch.full((2,), 7.0))
+    back = fp.to_tree()
+    assert isinstance(back["a"], NT) and isinstance(back["b"], list)
+    assert [n for n, _ in fp.named_views()] == ["a.u", "a.v", "b.0"]
+    other = fp.like(torch.zeros(9))
+    assert other.getaxes() == fp.getaxes() and torch.equal(other.a.u, torch.zeros(2, 3))
+    with pytest.raises(AttributeError):
+        fp.nope
+    aligned = fm.FlatParams.from_tree(tree, align_elems=4)
+    assert aligned.axes.entries["a"].entries["v"][0] == 8
+
+
+# ------------------------------------------------------------------------------ prefs / data
+def test_preferences_roundtrip(tmp_path, monkeypatch):
+    f = tmp_path / "LocalPreferences.toml"
+    f.write_text('[Other]\nkeep = 1\n')
+    monkeypatch.setenv("FMPI_PREFS_FILE", str(f))
+    assert prefs.load_preference(prefs.KEY_DISABLE_P2P, False) is False
+    fm.disable_p2p_support()
+    assert prefs.load_preference(prefs.KEY_DISABLE_P2P, False) is True
+    assert prefs.load_all()["Other"]["keep"] == 1
+    fm.disable_cudampi_support(disable=False)             # reference name kept as alias
+    assert prefs.load_preference(prefs.KEY_DISABLE_P2P, True) is False
+
+
+@pytest.mark.parametrize("n,w", [(10, 2), (10, 3), (10, 4), (9, 4), (1, 3), (0, 2), (16, 8)])
+def test_ddc_block_partition(n, w):
+    data = list(range(n))
+    shards = [fm.DistributedDataContainer(data, rank=r, world=w) for r in range(w)]
+    per = math.ceil(n / w) if n else 0
+    assert [x for s in shards for x in s] == data                  # disjoint cover, rank order
+    for r, s in enumerate(shards):
+        assert len(s) == max(0, min(per, n - r * per))
+        assert all(s[i] == data[s.idxs[i]] for i in range(len(s)))
+
+
+def test_not_initialized_error():
+    if fm.Initialized():
+        pytest.skip("world already up in this process")
+    with pytest.raises(fm.FluxMPINotInitializedError):
+        fm.local_rank()
+    with pytest.raises(fm.FluxMPINotInitializedError):
+        fm.allreduce_(torch.ones(1), "sum")
+
+
+def test_launcher_propagates_exit_code(tmp_path):
+    from fluxmpi_b200.launch import launch
+    s = tmp_path / "s.py"
+    s.write_text("import os, sys, time\nif os.environ['RANK']=='1': sys.exit(7)\ntime.sleep(60)\n")
+    code, _ = launch(3, [str(s)], timeout=30, capture=True)
+    assert code == 7
