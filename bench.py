@@ -1,0 +1,426 @@
+#!/usr/bin/env python
+"""Headline benchmark: ResNet-50 images/s, synthetic 224x224 ImageNet-shape data, data-parallel
+(BASELINE.json: "ResNet-50 img/s at 1/2/4/8 B200"; config 2).
+
+    python bench.py --gpus N --steps K --warmup W            # N == 1
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+Arms (--impl):
+  ours       this framework: DataParallelEngine (flat symmetric buffers, fused NVLink
+             all-reduce + Adam kernel per bucket overlapped with backward, whole step in one
+             CUDA graph), DeviceLoader (pinned double-buffered H2D), DistributedDataContainer.
+  reference  the UNMODIFIED reference from baseline/_ref — FluxMPI.jl is a Julia package; this
+             image has no Julia and no MPI, so the arm reports {"unavailable": ...}.
+  ddp        the operative baseline named by BASELINE.json's fallback: torch DDP + NCCL +
+             torch.optim.Adam(fused=True), same model / dtype / input pipeline, stock eager path.
+
+One JSON line on rank 0. `value` = whole-job images/s over the device-timed steps (CUDA events,
+max over ranks); `e2e` = the same through the public API with a pinned-host→device copy of every
+step's inputs and a device→host read of every step's loss inside the timed region.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "ddp"])
+    ap.add_argument("--model", default="resnet50", choices=["resnet50", "resnet_tiny"])
+    ap.add_argument("--batch", type=int, default=256, help="per-GPU batch (weak scaling)")
+    ap.add_argument("--image", type=int, default=224)
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--bucket-mb", type=float, default=32.0)
+    ap.add_argument("--algo", default="auto")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines: list[str] = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._drain, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _drain(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=3)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2])); pw.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------ shared pieces
+def make_model(name):
+    from fluxmpi_b200.models import resnet50, resnet_tiny
+    return resnet50() if name == "resnet50" else resnet_tiny(1000)
+
+
+def host_dataset(n_batches: int, batch: int, image: int, seed: int):
+    """Synthetic ImageNet-shaped samples in host memory: uint8 NHWC images + int64 labels."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    n = n_batches * batch
+    x = torch.randint(0, 256, (n, image, image, 3), dtype=torch.uint8, generator=g)
+    y = torch.randint(0, 1000, (n,), dtype=torch.int64, generator=g)
+    return x, y
+
+
+class RankLocalBlock:
+    """Global index space of ``world * len(local)`` samples of which only this rank's
+    contiguous block is resident (the block DistributedDataContainer assigns to it)."""
+
+    def __init__(self, local, rank: int, world: int):
+        self.local, self.n = local, len(local)
+        self.lo, self.total = rank * self.n, world * self.n
+
+    def __len__(self):
+        return self.total
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            s = range(self.total)[i]
+            return self.local[slice(s.start - self.lo, s.stop - self.lo, s.step)]
+        if isinstance(i, (list, tuple)):
+            return self.local[[j - self.lo for j in i]]
+        return self.local[i - self.lo]
+
+
+def preprocess(xb, dtype):
+    """uint8 NHWC -> normalised channels_last float tensor (a view permute, no extra copy)."""
+    import torch
+    x = xb.permute(0, 3, 1, 2)                     # NCHW view over NHWC memory == channels_last
+    return x.to(dtype).sub_(127.5).mul_(1.0 / 58.0)
+
+
+def baseline_number(model: str, n: int):
+    p = ROOT / "baseline" / "ddp_measured.json"
+    if not p.exists():
+        return None
+    try:
+        return json.loads(p.read_text()).get(model, {}).get(str(n))
+    except (ValueError, OSError):
+        return None
+
+
+def dist_max(value: float, impl: str) -> float:
+    """max over ranks of a python float"""
+    import torch
+    if int(os.environ.get("WORLD_SIZE", "1")) == 1:
+        return value
+    if impl == "ours":
+        import fluxmpi_b200 as fm
+        t = torch.tensor([value], dtype=torch.float64)
+        fm.allreduce_(t, "max")
+        return float(t)
+    import torch.distributed as dist
+    t = torch.tensor([value], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t)
+
+
+def timed(run_steps, k: int, barrier, impl: str):
+    """barrier + sync, K steps between CUDA events, sync + barrier; returns max-over-ranks ms."""
+    import torch
+    barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    run_steps(k)
+    e1.record()
+    torch.cuda.synchronize()
+    barrier()
+    return dist_max(e0.elapsed_time(e1), impl)
+
+
+# ------------------------------------------------------------------------------ our arm
+def run_ours(a):
+    import torch
+    import fluxmpi_b200 as fm
+    from fluxmpi_b200 import _native
+    from fluxmpi_b200 import rules as R
+    from fluxmpi_b200.parallel.engine import DataParallelEngine, GraphedStep
+
+    torch.backends.cudnn.benchmark = True
+    fm.Init()
+    rank, world = fm.local_rank(), fm.total_workers()
+    assert world == a.gpus, f"--gpus {a.gpus} but WORLD_SIZE={world}"
+    dev = fm.current_device()
+    cdt = torch.bfloat16 if a.dtype == "bf16" else torch.float32
+
+    torch.manual_seed(rank)
+    model = make_model(a.model).to(dev).to(memory_format=torch.channels_last)
+    engine = DataParallelEngine(model, fm.DistributedOptimizer(R.Adam(1e-3)), bucket_mb=a.bucket_mb,
+                                overlap=not a.no_overlap, algo=a.algo)
+    inv_w = 1.0 / world                        # reference semantics: SUM, loss scaled by 1/W
+
+    def step_fn(xb, yb):
+        x = preprocess(xb, torch.float32)
+        with torch.autocast("cuda", dtype=cdt, enabled=a.dtype == "bf16"):
+            loss = torch.nn.functional.cross_entropy(model(x), yb) * inv_w
+        loss.backward()
+        return loss
+
+    nb = 4
+    hx, hy = host_dataset(nb, a.batch, a.image, seed=1000 + rank)
+    # A global dataset of world * nb batches, sharded by DistributedDataContainer into
+    # contiguous rank-ordered blocks (weak scaling: per-GPU work is fixed). Like any lazily
+    # loaded dataset each process only materialises the samples of its own block.
+    data = fm.DistributedDataContainer(
+        RankLocalBlock(fm.TensorDataset(hx.pin_memory(), hy.pin_memory()), rank, world))
+    assert len(data) == nb * a.batch
+    loader = fm.DeviceLoader(data, a.batch, device=dev, depth=3)
+
+    first = next(iter(loader))
+    if a.no_graph:
+        def do_step(xb, yb):
+            loss = step_fn(xb, yb)
+            engine.step()
+            return loss
+        for _ in range(a.warmup):
+            do_step(*first)
+    else:
+        do_step = GraphedStep(engine, step_fn, first, warmup=max(a.warmup, 3))
+    torch.cuda.synchronize()
+
+    # ---- device-timed: inputs resident on the device
+    dx, dy = first[0].clone(), first[1].clone()
+
+    def device_steps(k):
+        for _ in range(k):
+            do_step(dx, dy)
+
+    device_steps(2)
+    sampler = ClockSampler(dev.index) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    before = _native.launch_count
+    ms = timed(device_steps, a.steps, fm.barrier, "ours")
+    launches = _native.launch_count - before
+
+    # ---- end to end through the public API: pinned host -> device every step, loss -> host
+    loss_host = torch.zeros(a.steps + 1, dtype=torch.float32).pin_memory()
+    d2h_stream = torch.cuda.Stream(dev)
+
+    def e2e_steps(k):
+        it = iter(loader)
+        done = 0
+        evs = []
+        while done < k:
+            try:
+                xb, yb = next(it)
+            except StopIteration:
+                it = iter(loader)
+                continue
+            loss = do_step(xb, yb)
+            ready = torch.cuda.Event()
+            ready.record()
+            with torch.cuda.stream(d2h_stream):
+                d2h_stream.wait_event(ready)
+                loss_host[done:done + 1].copy_(loss.detach().float().reshape(1), non_blocking=True)
+            if evs:
+                evs.pop(0).synchronize()          # the host reads step k-1's loss while step k runs
+            e = torch.cuda.Event()
+            e.record(d2h_stream)
+            evs.append(e)
+            done += 1
+        for e in evs:
+            e.synchronize()
+        torch.cuda.current_stream().wait_stream(d2h_stream)
+
+    e2e_steps(2)
+    h2d0 = loader.h2d_bytes
+    ms_e2e = timed(e2e_steps, a.steps, fm.barrier, "ours")
+    h2d_per_step = (loader.h2d_bytes - h2d0) / max(a.steps, 1)
+    clocks = sampler.stop() if sampler else None
+    final_loss = float(loss_host[a.steps - 1])
+
+    gb = a.batch * world
+    value = gb * a.steps / (ms / 1e3)
+    e2e = gb * a.steps / (ms_e2e / 1e3)
+    base = baseline_number(a.model, world)
+    dw = fm.runtime.state().device_world
+    if rank == 0:
+        print(json.dumps({
+            "metric": "ResNet-50 train images/s (synthetic 224x224, data-parallel)", "impl": "ours",
+            "value": round(value, 1), "unit": "img/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": round(ms / a.steps, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": round(value / base, 4) if base else None, "dtype": a.dtype, "data": "synthetic",
+            "config": {"model": a.model, "global_batch": gb, "per_gpu_batch": a.batch, "image": a.image,
+                       "seq_len": None, "parallelism": f"dp{world}", "optimizer": "Adam(1e-3), fused with the gradient all-reduce",
+                       "layout": "channels_last", "cuda_graph": not a.no_graph, "overlap": not a.no_overlap,
+                       "bucket_mb": a.bucket_mb, "buckets": len(engine.buckets),
+                       "comm": f"{dw.mode}{'+nvls' if engine.algo == _native.ALGO_NVLS else ''}",
+                       "l2": "per-step working set (activations of 256 images + 205 MB of parameters and gradients) far exceeds the 126 MB L2; no explicit flush",
+                       "baseline": "vs_baseline divides by baseline/ddp_measured.json (torch DDP+NCCL, our measurement); the reference publishes no number"},
+            "e2e": {"value": round(e2e, 1), "unit": "img/s", "ms_per_step": round(ms_e2e / a.steps, 3),
+                    "h2d_bytes_per_step": int(h2d_per_step), "d2h_bytes_per_step": 4},
+            "gpu_launches": int(launches), "final_loss": final_loss, "clocks": clocks}))
+    engine.close()
+    fm.Finalize()
+
+
+# ------------------------------------------------------------------------------ DDP + NCCL arm
+def run_ddp(a):
+    import torch
+    import torch.distributed as dist
+    from torch.nn.parallel import DistributedDataParallel as DDP
+
+    torch.backends.cudnn.benchmark = True
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    lrank = int(os.environ.get("LOCAL_RANK", rank))
+    assert world == a.gpus, f"--gpus {a.gpus} but WORLD_SIZE={world}"
+    torch.cuda.set_device(lrank)
+    dev = torch.device("cuda", lrank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    cdt = torch.bfloat16 if a.dtype == "bf16" else torch.float32
+    torch.manual_seed(0)
+    model = make_model(a.model).to(dev).to(memory_format=torch.channels_last)
+    net = DDP(model, device_ids=[lrank], gradient_as_bucket_view=True) if world > 1 else model
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3, fused=True)
+
+    def do_step(xb, yb):
+        x = preprocess(xb, torch.float32)
+        with torch.autocast("cuda", dtype=cdt, enabled=a.dtype == "bf16"):
+            loss = torch.nn.functional.cross_entropy(net(x), yb)
+        opt.zero_grad(set_to_none=True)
+        loss.backward()
+        opt.step()
+        return loss
+
+    nb = 4
+    hx, hy = host_dataset(nb, a.batch, a.image, seed=1000 + rank)
+    hx, hy = hx.pin_memory(), hy.pin_memory()
+    dx, dy = hx[:a.batch].to(dev), hy[:a.batch].to(dev)
+    barrier = (lambda: dist.barrier()) if world > 1 else (lambda: None)
+    for _ in range(max(a.warmup, 3)):
+        do_step(dx, dy)
+    torch.cuda.synchronize()
+
+    def device_steps(k):
+        for _ in range(k):
+            do_step(dx, dy)
+
+    sampler = ClockSampler(lrank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    ms = timed(device_steps, a.steps, barrier, "ddp")
+
+    copy_stream = torch.cuda.Stream(dev)
+    bufs = [(torch.empty_like(dx), torch.empty_like(dy)) for _ in range(2)]
+    loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+
+    def e2e_steps(k):
+        # standard prefetching loop: copy batch i+1 on a side stream while batch i computes
+        def stage(i):
+            s = i % nb
+            xb, yb = bufs[i % 2]
+            with torch.cuda.stream(copy_stream):
+                xb.copy_(hx[s * a.batch:(s + 1) * a.batch], non_blocking=True)
+                yb.copy_(hy[s * a.batch:(s + 1) * a.batch], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy_stream)
+            return ev
+        ev = stage(0)
+        used = [None, None]                       # "compute finished with this buffer" events
+        for i in range(k):
+            torch.cuda.current_stream().wait_event(ev)
+            if i + 1 < k:
+                if used[(i + 1) % 2] is not None:
+                    copy_stream.wait_event(used[(i + 1) % 2])
+                ev = stage(i + 1)                 # overlaps with this step's compute
+            xb, yb = bufs[i % 2]
+            loss = do_step(xb, yb)
+            used[i % 2] = torch.cuda.Event()
+            used[i % 2].record()
+            loss_host.copy_(loss.detach().float().reshape(1), non_blocking=True)
+        torch.cuda.synchronize()
+
+    e2e_steps(2)
+    ms_e2e = timed(e2e_steps, a.steps, barrier, "ddp")
+    clocks = sampler.stop() if sampler else None
+    gb = a.batch * world
+    value = gb * a.steps / (ms / 1e3)
+    if rank == 0:
+        print(json.dumps({
+            "metric": "ResNet-50 train images/s (synthetic 224x224, data-parallel)", "impl": "ddp",
+            "value": round(value, 1), "unit": "img/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": round(ms / a.steps, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
+            "config": {"model": a.model, "global_batch": gb, "per_gpu_batch": a.batch, "image": a.image,
+                       "parallelism": f"dp{world}", "optimizer": "torch.optim.Adam(fused=True)",
+                       "layout": "channels_last", "comm": "NCCL (torch DDP, gradient_as_bucket_view)"},
+            "e2e": {"value": round(gb * a.steps / (ms_e2e / 1e3), 1), "unit": "img/s",
+                    "h2d_bytes_per_step": int(a.batch * (a.image * a.image * 3 + 8)), "d2h_bytes_per_step": 4},
+            "gpu_launches": 0, "final_loss": float(loss_host[0]), "clocks": clocks}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_reference(a):
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(json.dumps({
+            "impl": "reference",
+            "unavailable": "nikopj/FluxMPI.jl is a pure-Julia package on MPI.jl: `pip install --target "
+                           "baseline/_ref /root/reference` fails (no setup.py/pyproject.toml) and this image "
+                           "has no julia, mpiexec or libmpi; see DESIGN.md (--impl ddp is the measured stand-in)"}))
+
+
+if __name__ == "__main__":
+    args = parse()
+    {"ours": run_ours, "ddp": run_ddp, "reference": run_reference}[args.impl](args)

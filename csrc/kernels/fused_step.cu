@@ -1,0 +1,346 @@
+// Fused gradient all-reduce (+) optimiser step — the headline kernel.
+//
+// Reference path being replaced (/root/reference/src/optimizer.jl:20-23): for every parameter
+// leaf, a blocking MPI_Allreduce of the gradient (staged D2H/H2D for CuArrays,
+// src/mpi_extensions.jl:97-106) followed by the wrapped rule's several elementwise GPU kernels
+// (Optimisers.apply! + subtract!). Here ONE launch per bucket does all
+// of it over NVLink:
+//
+//   start barrier                      (every rank's backward has produced this bucket)
+//   rank r, for its 1/W slice:         g = sum over ranks of peer gradients   (rank order, fp32)
+//                                      rule update of m, v, (master) p in registers
+//                                      store new p into EVERY rank's parameter window
+//   end barrier                        (all parameter stores have landed)
+//   optional: clear the local gradient bucket for the next accumulation
+//
+// Link traffic per rank and direction: (W-1)/W * N gradient bytes in + (W-1)/W * N parameter
+// bytes in — the same as a two-shot all-reduce — but the optimiser's HBM traffic drops from
+// 28 B/element to ~8 + 20/W B/element, the reduced gradient never exists in memory, and the
+// moments are only ever touched by their owner (lazily replicated, see parallel/engine.py).
+// One owner computes each parameter => replicas stay bit-identical.
+//
+// kNvls = true uses the NVSwitch's in-fabric reduction instead of W peer loads
+// (multimem.ld_reduce) and its multicast store instead of W peer stores (multimem.st).
+#include "common.cuh"
+
+namespace fmpi {
+
+struct FusedArgs {
+  uint64_t g_off, p_off;  // byte offsets of the flat gradient / parameter buffers in the window
+  float* m[FMPI_MAX_RANKS];
+  float* v[FMPI_MAX_RANKS];
+  float* master[FMPI_MAX_RANKS];
+  const int64_t* step[FMPI_MAX_RANKS];
+  uint64_t lo, hi;  // element range of this bucket
+  fmpi_hyper h;
+};
+
+template <int kRule>
+struct RuleMath {
+  float eta, b1, b2, eps, lambda, rho, bc1, bc2, gscale;
+  __device__ __forceinline__ void init(const fmpi_hyper& h, int64_t t) {
+    eta = h.eta_dev ? *reinterpret_cast<const float*>(h.eta_dev) : h.eta;
+    b1 = h.beta1; b2 = h.beta2; eps = h.eps; lambda = h.lambda; rho = h.rho;
+    gscale = h.grad_scale;
+    if (kRule == FMPI_RULE_ADAM || kRule == FMPI_RULE_ADAMW) {
+      const float n = float(t + 1);
+      bc1 = 1.f - powf(b1, n);
+      bc2 = 1.f - powf(b2, n);
+    } else {
+      bc1 = bc2 = 1.f;
+    }
+  }
+  // returns the new parameter; updates m, v in place
+  __device__ __forceinline__ float step(float p, float g, float& m, float& v) const {
+    g *= gscale;
+    if (kRule == FMPI_RULE_DESCENT) {
+      return p - eta * g;
+    } else if (kRule == FMPI_RULE_MOMENTUM) {
+      m = rho * m + eta * g;
+      return p - m;
+    } else if (kRule == FMPI_RULE_NESTEROV) {
+      const float d = -rho * rho * m + (1.f + rho) * eta * g;
+      m = rho * m - eta * g;
+      return p - d;
+    } else {
+      m = b1 * m + (1.f - b1) * g;
+      v = b2 * v + (1.f - b2) * g * g;
+      const float d = (m / bc1) / (sqrtf(v / bc2) + eps) * eta;
+      if (kRule == FMPI_RULE_ADAMW) return p - (d + lambda * p);
+      return p - d;
+    }
+  }
+};
+
+template <int kRule> struct RuleState { static constexpr bool kM = true, kV = false; };
+template <> struct RuleState<FMPI_RULE_DESCENT> { static constexpr bool kM = false, kV = false; };
+template <> struct RuleState<FMPI_RULE_ADAM> { static constexpr bool kM = true, kV = true; };
+template <> struct RuleState<FMPI_RULE_ADAMW> { static constexpr bool kM = true, kV = true; };
+
+// ---- in-switch reduction / multicast store (NVLS)
+template <typename T> struct Multimem;
+template <> struct Multimem<float> {
+  __device__ static uint4 ld_reduce(const void* mc) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+    return v;
+  }
+};
+template <> struct Multimem<__nv_bfloat16> {
+  __device__ static uint4 ld_reduce(const void* mc) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+    return v;
+  }
+};
+template <> struct Multimem<__half> {
+  __device__ static uint4 ld_reduce(const void* mc) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+    return v;
+  }
+};
+__device__ __forceinline__ void multimem_st(void* mc, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+template <typename T, bool kMaster, int kRule, bool kNvls>
+__global__ void __launch_bounds__(512)
+fused_step_kernel(fmpi_devcomm c, FusedArgs a) {
+  using V = VecOps<T>;
+  constexpr int N = V::kN;
+  Ctx x;
+  const bool multi = c.world > 1;
+  if (multi) {
+    ctx_init(x, c);
+    block_barrier(x, c);
+  } else {
+    x.rank = 0;
+    x.world = 1;
+  }
+  const int ai = arg_index(c);
+  RuleMath<kRule> rule;
+  rule.init(a.h, a.step[ai] ? *a.step[ai] : 0);
+
+  const uint64_t nvec = (a.hi - a.lo) / N;
+  const uint64_t per = (nvec + c.world - 1) / c.world;
+  const uint64_t vlo = min(per * x.rank, nvec), vhi = min(vlo + per, nvec);
+  const uint64_t gbase = a.g_off + a.lo * sizeof(T), pbase = a.p_off + a.lo * sizeof(T);
+  float* __restrict__ mloc = a.m[ai];
+  float* __restrict__ vloc = a.v[ai];
+  float* __restrict__ mst = a.master[ai];
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+
+  for (uint64_t i = vlo + uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < vhi; i += stride) {
+    // ---- reduced gradient, fp32, rank order
+    float g[N];
+    if (kNvls) {
+      V::unpack(Multimem<T>::ld_reduce(byte_ptr(c.mc_data, gbase) + i * 16), g);
+    } else {
+      uint4 raw[FMPI_MAX_RANKS];
+#pragma unroll
+      for (int r = 0; r < FMPI_MAX_RANKS; ++r)
+        if (r < c.world) raw[r] = ld_stream(byte_ptr(c.data[r], gbase) + i * 16);
+      V::unpack(raw[0], g);
+#pragma unroll
+      for (int r = 1; r < FMPI_MAX_RANKS; ++r)
+        if (r < c.world) {
+          float b[N];
+          V::unpack(raw[r], b);
+#pragma unroll
+          for (int k = 0; k < N; ++k) g[k] += b[k];
+        }
+    }
+    // ---- local state
+    const uint64_t e = a.lo + i * N;  // first element index
+    float p[N], m[N], v[N];
+    if (kMaster) {
+#pragma unroll
+      for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(p + k) = *reinterpret_cast<const float4*>(mst + e + k);
+    } else {
+      V::unpack(ld_stream(byte_ptr(c.data[x.rank], pbase) + i * 16), p);
+    }
+    if (RuleState<kRule>::kM) {
+#pragma unroll
+      for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(m + k) = *reinterpret_cast<const float4*>(mloc + e + k);
+    }
+    if (RuleState<kRule>::kV) {
+#pragma unroll
+      for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(v + k) = *reinterpret_cast<const float4*>(vloc + e + k);
+    }
+    // ---- rule
+#pragma unroll
+    for (int k = 0; k < N; ++k) p[k] = rule.step(p[k], g[k], m[k], v[k]);
+    // ---- write back
+    if (RuleState<kRule>::kM) {
+#pragma unroll
+      for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(mloc + e + k) = *reinterpret_cast<float4*>(m + k);
+    }
+    if (RuleState<kRule>::kV) {
+#pragma unroll
+      for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(vloc + e + k) = *reinterpret_cast<float4*>(v + k);
+    }
+    if (kMaster) {
+#pragma unroll
+      for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(mst + e + k) = *reinterpret_cast<float4*>(p + k);
+    }
+    const uint4 pv = V::pack(p);
+    if (kNvls) {
+      multimem_st(byte_ptr(c.mc_data, pbase) + i * 16, pv);
+    } else {
+#pragma unroll
+      for (int r = 0; r < FMPI_MAX_RANKS; ++r)
+        if (r < c.world) st_stream(byte_ptr(c.data[r], pbase) + i * 16, pv);
+    }
+  }
+
+  if (multi) {
+    block_barrier(x, c);
+    ctx_finish(x);
+  }
+  if (a.h.zero_grad) {
+    // Clear with the readers' block->vector mapping, slice by slice: vector i of slice q was
+    // read by block blockIdx.x of rank q, and that is exactly the block the barrier above
+    // synchronised with.
+    uint4* gl = reinterpret_cast<uint4*>(byte_ptr(c.data[x.rank], gbase));
+    for (int q = 0; q < c.world; ++q) {
+      const uint64_t qlo = min(per * q, nvec), qhi = min(qlo + per, nvec);
+      for (uint64_t i = qlo + uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < qhi; i += stride)
+        gl[i] = make_uint4(0, 0, 0, 0);
+    }
+  }
+}
+
+__global__ void step_advance_kernel(int64_t* s) { *s += 1; }
+
+}  // namespace fmpi
+
+using namespace fmpi;
+using fmpi_host::check_cuda;
+using fmpi_host::launch_ranked;
+using fmpi_host::set_error;
+
+namespace {
+
+template <typename T, bool kMaster, bool kNvls>
+int launch_rule(const fmpi_devcomm& c, const FusedArgs& a, int blocks, int threads, cudaStream_t st) {
+  switch (a.h.rule) {
+    case FMPI_RULE_DESCENT:
+      return launch_ranked(fused_step_kernel<T, kMaster, FMPI_RULE_DESCENT, kNvls>, c, blocks, threads, st, c, a);
+    case FMPI_RULE_MOMENTUM:
+      return launch_ranked(fused_step_kernel<T, kMaster, FMPI_RULE_MOMENTUM, kNvls>, c, blocks, threads, st, c, a);
+    case FMPI_RULE_NESTEROV:
+      return launch_ranked(fused_step_kernel<T, kMaster, FMPI_RULE_NESTEROV, kNvls>, c, blocks, threads, st, c, a);
+    case FMPI_RULE_ADAM:
+      return launch_ranked(fused_step_kernel<T, kMaster, FMPI_RULE_ADAM, kNvls>, c, blocks, threads, st, c, a);
+    case FMPI_RULE_ADAMW:
+      return launch_ranked(fused_step_kernel<T, kMaster, FMPI_RULE_ADAMW, kNvls>, c, blocks, threads, st, c, a);
+    default:
+      return set_error("rule %d has no fused kernel", a.h.rule);
+  }
+}
+
+template <typename T, bool kNvls>
+int launch_master(const fmpi_devcomm& c, const FusedArgs& a, bool master, int blocks, int threads,
+                  cudaStream_t st) {
+  return master ? launch_rule<T, true, kNvls>(c, a, blocks, threads, st)
+                : launch_rule<T, false, kNvls>(c, a, blocks, threads, st);
+}
+
+}  // namespace
+
+extern "C" {
+
+int fmpi_fused_step(const fmpi_devcomm* c, uint64_t g_off, int gdt, uint64_t p_off, int pdt,
+                    float* const* m, float* const* v, float* const* master, uint64_t lo,
+                    uint64_t hi, const fmpi_hyper* h, const int64_t* const* step_dev,
+                    const fmpi_launch* l, fmpi_stream stream) {
+  if (!c || !h) return set_error("null argument");
+  if (c->world < 1 || c->world > FMPI_MAX_RANKS) return set_error("world %d out of range", c->world);
+  if (gdt != pdt) return set_error("fused step needs gradients and parameters of one dtype");
+  if (gdt != FMPI_F32 && gdt != FMPI_BF16 && gdt != FMPI_F16)
+    return set_error("fused step supports f32 / bf16 / f16, got dtype %d", gdt);
+  const uint64_t es = dtype_size(gdt), N = 16 / es;
+  if (hi < lo) return set_error("bad bucket range");
+  if (hi == lo) return 0;
+  if ((g_off % 16) || (p_off % 16) || (lo % N) || ((hi - lo) % N))
+    return set_error("bucket [%llu, %llu) / offsets must be 16-byte aligned",
+                     (unsigned long long)lo, (unsigned long long)hi);
+  if (g_off + hi * es > c->data_bytes || p_off + hi * es > c->data_bytes)
+    return set_error("bucket exceeds the symmetric window");
+  const int n_ranks = c->emulate ? c->world : 1;
+  FusedArgs a{};
+  a.g_off = g_off; a.p_off = p_off; a.lo = lo; a.hi = hi; a.h = *h;
+  const bool need_m = h->rule != FMPI_RULE_DESCENT;
+  const bool need_v = h->rule == FMPI_RULE_ADAM || h->rule == FMPI_RULE_ADAMW;
+  for (int i = 0; i < n_ranks; ++i) {
+    a.m[i] = m ? m[i] : nullptr;
+    a.v[i] = v ? v[i] : nullptr;
+    a.master[i] = master ? master[i] : nullptr;
+    a.step[i] = step_dev ? step_dev[i] : nullptr;
+    if ((need_m && !a.m[i]) || (need_v && !a.v[i])) return set_error("rule %d needs moment buffers", h->rule);
+  }
+  const bool use_master = master && master[0];
+  if (gdt == FMPI_F32 && use_master) return set_error("fp32 parameters take no master copy");
+  const int algo = l ? l->algo : FMPI_ALGO_AUTO;
+  const bool nvls = algo == FMPI_ALGO_NVLS && c->world > 1;
+  if (nvls && (!c->mc_data || c->emulate)) return set_error("NVLS requested but no multicast mapping");
+
+  const uint64_t slice_bytes = (hi - lo) * es / c->world;
+  int threads = (l && l->threads > 0) ? l->threads : 512;
+  if (threads > 512) threads = 512;
+  int blocks;
+  if (l && l->blocks > 0) {
+    blocks = l->blocks;
+  } else {
+    const uint64_t per_block = uint64_t(threads) * 16 * 2;
+    const uint64_t want = (slice_bytes + per_block - 1) / per_block;
+    const uint64_t cap = c->world == 1 ? 148 * 4 : 148;
+    blocks = int(want < 1 ? 1 : want > cap ? cap : want);
+  }
+  if (c->world > 1 && blocks > FMPI_MAX_BLOCKS) blocks = FMPI_MAX_BLOCKS;
+  if (c->emulate && blocks > 128 / c->world) blocks = 128 / c->world;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+  if (c->world == 1) {
+    // no peers: plain launch, any grid size (launch_ranked clamps to the signal-pad rows)
+    fmpi_devcomm c1 = *c;
+    c1.emulate = 0;
+    c1.rank = 0;
+#define FMPI_W1(T, MASTER)                                                                      \
+  switch (h->rule) {                                                                            \
+    case FMPI_RULE_DESCENT: fused_step_kernel<T, MASTER, FMPI_RULE_DESCENT, false><<<blocks, threads, 0, st>>>(c1, a); break;   \
+    case FMPI_RULE_MOMENTUM: fused_step_kernel<T, MASTER, FMPI_RULE_MOMENTUM, false><<<blocks, threads, 0, st>>>(c1, a); break; \
+    case FMPI_RULE_NESTEROV: fused_step_kernel<T, MASTER, FMPI_RULE_NESTEROV, false><<<blocks, threads, 0, st>>>(c1, a); break; \
+    case FMPI_RULE_ADAM: fused_step_kernel<T, MASTER, FMPI_RULE_ADAM, false><<<blocks, threads, 0, st>>>(c1, a); break;         \
+    case FMPI_RULE_ADAMW: fused_step_kernel<T, MASTER, FMPI_RULE_ADAMW, false><<<blocks, threads, 0, st>>>(c1, a); break;       \
+    default: return set_error("rule %d has no fused kernel", h->rule);                          \
+  }
+    if (gdt == FMPI_F32) { FMPI_W1(float, false) }
+    else if (gdt == FMPI_BF16) { if (use_master) { FMPI_W1(__nv_bfloat16, true) } else { FMPI_W1(__nv_bfloat16, false) } }
+    else { if (use_master) { FMPI_W1(__half, true) } else { FMPI_W1(__half, false) } }
+#undef FMPI_W1
+    return check_cuda(cudaGetLastError(), "fused_step launch");
+  }
+
+  if (gdt == FMPI_F32)
+    return nvls ? launch_rule<float, false, true>(*c, a, blocks, threads, st)
+                : launch_rule<float, false, false>(*c, a, blocks, threads, st);
+  if (gdt == FMPI_BF16)
+    return nvls ? launch_master<__nv_bfloat16, true>(*c, a, use_master, blocks, threads, st)
+                : launch_master<__nv_bfloat16, false>(*c, a, use_master, blocks, threads, st);
+  return nvls ? launch_master<__half, true>(*c, a, use_master, blocks, threads, st)
+              : launch_master<__half, false>(*c, a, use_master, blocks, threads, st);
+}
+
+int fmpi_step_advance(int64_t* step_dev, fmpi_stream st) {
+  if (!step_dev) return set_error("null step counter");
+  step_advance_kernel<<<1, 1, 0, static_cast<cudaStream_t>(st)>>>(step_dev);
+  return check_cuda(cudaGetLastError(), "step_advance");
+}
+
+}  // extern "C"

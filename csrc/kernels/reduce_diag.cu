@@ -1,0 +1,153 @@
+// Diagnostics on flat buffers: sum of squares (global gradient norm for logging / clipping)
+// and a 64-bit checksum (bitwise replica-consistency assertions, SURVEY §5.1 — the reference
+// has no such check; its tests compare values rank by rank, test/test_synchronize.jl).
+//
+// Both are single-launch two-stage reductions: every block writes one partial into a scratch
+// buffer, takes a ticket, and the last block to arrive folds the partials in index order, so
+// the result is deterministic run to run. The scratch buffer (fmpi_reduce_scratch_bytes(),
+// caller-allocated, zero-initialised once) holds the ticket word and the partials; the ticket
+// is reset by the last block so the buffer can be reused by the next call on the same stream.
+#include "common.cuh"
+
+namespace fmpi {
+
+constexpr int kMaxPartials = 1024;
+constexpr size_t kScratchBytes = 16 + sizeof(double) * kMaxPartials;
+
+template <typename T> __device__ __forceinline__ double to_double(T x) { return double(x); }
+template <> __device__ __forceinline__ double to_double(__nv_bfloat16 x) { return double(__bfloat162float(x)); }
+template <> __device__ __forceinline__ double to_double(__half x) { return double(__half2float(x)); }
+
+__device__ __forceinline__ double block_sum(double v, double* sh) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) sh[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    v = lane < (blockDim.x + 31) / 32 ? sh[lane] : 0.0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  }
+  return v;  // valid in thread 0
+}
+
+__device__ __forceinline__ uint64_t block_sum_u64(uint64_t v, uint64_t* sh) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) sh[warp] = v;
+  __syncthreads();
+  if (warp == 0) {
+    v = lane < (blockDim.x + 31) / 32 ? sh[lane] : 0ull;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+  }
+  return v;
+}
+
+// Returns true in thread 0 of the last block to finish.
+__device__ __forceinline__ bool take_ticket(unsigned int* ticket) {
+  __shared__ bool last;
+  if (threadIdx.x == 0) {
+    __threadfence();
+    last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  return last;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(512)
+sumsq_kernel(const T* __restrict__ x, uint64_t n, double* out, unsigned int* ticket, double* partials) {
+  __shared__ double sh[32];
+  double acc = 0.0;
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double v = to_double(x[i]);
+    acc += v * v;
+  }
+  acc = block_sum(acc, sh);
+  if (threadIdx.x == 0) partials[blockIdx.x] = acc;
+  if (take_ticket(ticket)) {
+    __threadfence();
+    double tot = 0.0;
+    for (int b = threadIdx.x; b < gridDim.x; b += blockDim.x) tot += partials[b];
+    __syncthreads();
+    tot = block_sum(tot, sh);
+    if (threadIdx.x == 0) {
+      *out = tot;
+      *ticket = 0;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(512)
+checksum_kernel(const uint8_t* __restrict__ x, uint64_t nbytes, uint64_t* out, unsigned int* ticket,
+                uint64_t* partials) {
+  __shared__ uint64_t sh[32];
+  uint64_t acc = 0;
+  const uint64_t nwords = nbytes / 4;
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(x);
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nwords; i += stride)
+    acc += (uint64_t(w[i]) + 0x9E3779B97F4A7C15ull) * (2 * i + 1);
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (uint64_t k = nwords * 4; k < nbytes; ++k) acc += (uint64_t(x[k]) + 0x51ull) * (2 * k + 1);
+  acc = block_sum_u64(acc, sh);
+  if (threadIdx.x == 0) partials[blockIdx.x] = acc;
+  if (take_ticket(ticket)) {
+    __threadfence();
+    uint64_t tot = 0;
+    for (int b = threadIdx.x; b < gridDim.x; b += blockDim.x) tot += partials[b];
+    __syncthreads();
+    tot = block_sum_u64(tot, sh);
+    if (threadIdx.x == 0) {
+      *out = tot;
+      *ticket = 0;
+    }
+  }
+}
+
+}  // namespace fmpi
+
+using namespace fmpi;
+using fmpi_host::check_cuda;
+using fmpi_host::set_error;
+
+static int diag_blocks(uint64_t n) {
+  const uint64_t want = (n + 512 * 8 - 1) / (512 * 8);
+  return int(want < 1 ? 1 : want > 148 * 4 ? 148 * 4 : want);
+}
+
+extern "C" {
+
+size_t fmpi_reduce_scratch_bytes(void) { return kScratchBytes; }
+
+int fmpi_sumsq(const void* x, uint64_t count, int dtype, double* out, void* scratch, fmpi_stream st) {
+  if (!out || !scratch) return set_error("null output / scratch");
+  unsigned int* ticket = static_cast<unsigned int*>(scratch);
+  double* partials = reinterpret_cast<double*>(static_cast<uint8_t*>(scratch) + 16);
+  const int blocks = diag_blocks(count);
+  cudaStream_t s = static_cast<cudaStream_t>(st);
+  switch (dtype) {
+    case FMPI_F32: sumsq_kernel<float><<<blocks, 512, 0, s>>>(static_cast<const float*>(x), count, out, ticket, partials); break;
+    case FMPI_F64: sumsq_kernel<double><<<blocks, 512, 0, s>>>(static_cast<const double*>(x), count, out, ticket, partials); break;
+    case FMPI_BF16: sumsq_kernel<__nv_bfloat16><<<blocks, 512, 0, s>>>(static_cast<const __nv_bfloat16*>(x), count, out, ticket, partials); break;
+    case FMPI_F16: sumsq_kernel<__half><<<blocks, 512, 0, s>>>(static_cast<const __half*>(x), count, out, ticket, partials); break;
+    default: return set_error("sumsq: unsupported dtype %d", dtype);
+  }
+  return check_cuda(cudaGetLastError(), "sumsq launch");
+}
+
+int fmpi_checksum(const void* x, uint64_t nbytes, uint64_t* out, void* scratch, fmpi_stream st) {
+  if (!out || !scratch) return set_error("null output / scratch");
+  if (reinterpret_cast<uintptr_t>(x) % 4) return set_error("checksum: buffer must be 4-byte aligned");
+  unsigned int* ticket = static_cast<unsigned int*>(scratch);
+  uint64_t* partials = reinterpret_cast<uint64_t*>(static_cast<uint8_t*>(scratch) + 16);
+  checksum_kernel<<<diag_blocks(nbytes / 4), 512, 0, static_cast<cudaStream_t>(st)>>>(
+      static_cast<const uint8_t*>(x), nbytes, out, ticket, partials);
+  return check_cuda(cudaGetLastError(), "checksum launch");
+}
+
+}  // extern "C"

@@ -122,6 +122,7 @@ class Hyper(C.Structure):
         ("lam", C.c_float), ("rho", C.c_float),
         ("grad_scale", C.c_float),
         ("zero_grad", C.c_int32),
+        ("eta_dev", C.c_uint64),
     ]
 
 

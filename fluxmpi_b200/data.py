@@ -38,14 +38,23 @@ class DistributedDataContainer:
         return len(self.idxs)
 
     def __getitem__(self, i):
+        """``ddc[i]`` = ``data[idxs[i]]`` (src/data.jl:26). Slices and index lists are forwarded
+        to the container in one call when it supports batch indexing (tensors, TensorDataset),
+        so a mini-batch is one gather instead of ``batch`` Python-level lookups."""
         if isinstance(i, slice):
-            return [self.data[j] for j in self.idxs[i]]
-        if isinstance(i, (list, tuple)):
-            return [self.data[self.idxs[j]] for j in i]
-        if isinstance(i, torch.Tensor):
-            if i.dim() == 0:
-                return self.data[self.idxs[int(i)]]
-            return [self.data[self.idxs[int(j)]] for j in i]
+            r = self.idxs[i]
+            try:
+                return self.data[slice(r.start, r.stop, r.step)] if len(r) else self.data[0:0]
+            except (TypeError, IndexError, KeyError):
+                return [self.data[j] for j in r]
+        if isinstance(i, torch.Tensor) and i.dim() == 0:
+            return self.data[self.idxs[int(i)]]
+        if isinstance(i, (list, tuple, torch.Tensor)):
+            mapped = [self.idxs[int(j)] for j in i]
+            try:
+                return self.data[mapped]
+            except (TypeError, IndexError, KeyError):
+                return [self.data[j] for j in mapped]
         return self.data[self.idxs[i]]
 
     def __iter__(self):
@@ -117,8 +126,12 @@ class DeviceLoader:
         return list(range(n))
 
     def _gather(self, idx: list[int]):
+        # a contiguous run (no shuffling) becomes a slice: tensor-backed containers then hand
+        # back views and the only host copy left is the one into the pinned slot
+        key = slice(idx[0], idx[-1] + 1) if idx and idx[-1] - idx[0] + 1 == len(idx) and \
+            all(b - a == 1 for a, b in zip(idx, idx[1:])) else idx
         try:
-            batch = self.data[idx]       # batch-indexable containers gather in one op
+            batch = self.data[key]       # batch-indexable containers gather in one op
             if isinstance(batch, list):
                 batch = _collate(batch)
         except (TypeError, IndexError, KeyError):
@@ -137,12 +150,17 @@ class DeviceLoader:
                                     for b in batch)
         if self._events[slot] is not None:
             self._events[slot].synchronize()     # pinned slot free to overwrite
-        for p, b in zip(self._pinned[slot], batch):
-            p.copy_(b)
+        # a batch that already sits contiguously in pinned memory (a view of a pinned dataset)
+        # is DMA'd from where it is; anything else is first assembled in the pinned slot
+        direct = all(b.is_pinned() and b.is_contiguous() for b in batch)
+        src = batch if direct else self._pinned[slot]
+        if not direct:
+            for p, b in zip(self._pinned[slot], batch):
+                p.copy_(b)
         with torch.cuda.stream(self._stream):
             if self._consumed[slot] is not None:
                 self._stream.wait_event(self._consumed[slot])   # device slot no longer in use
-            for d, p in zip(self._dev[slot], self._pinned[slot]):
+            for d, p in zip(self._dev[slot], src):
                 d.copy_(p, non_blocking=True)
                 self.h2d_bytes += p.numel() * p.element_size()
             ev = torch.cuda.Event()

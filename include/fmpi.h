@@ -188,7 +188,9 @@ typedef struct {
   int32_t rule;          /* fmpi_rule */
   float eta, beta1, beta2, eps, lambda, rho;
   float grad_scale;      /* multiplies the summed gradient (1 = reference SUM semantics) */
-  int32_t zero_grad;     /* != 0: owner clears every rank's gradient slice after reading it */
+  int32_t zero_grad;     /* != 0: each rank clears its gradient bucket after the end barrier */
+  uint64_t eta_dev;      /* optional device pointer to a float that overrides eta (learning-rate
+                            schedules under CUDA-graph replay); 0 = use eta */
 } fmpi_hyper;
 
 int fmpi_fused_step(const fmpi_devcomm* c, uint64_t g_off, int gdt, uint64_t p_off, int pdt,

@@ -1,0 +1,200 @@
+"""GPU tests of the training path through the public API on one B200 (world of one; the
+multi-rank device code is covered in emulation by test_gpu_kernels.py and on real GPUs by
+test_gpu_multi.py)."""
+import copy
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+if not torch.cuda.is_available():
+    pytest.skip("needs a CUDA device", allow_module_level=True)
+
+import fluxmpi_b200 as fm
+from fluxmpi_b200 import _native
+from fluxmpi_b200 import rules as R
+from fluxmpi_b200.models import resnet_tiny, vit_tiny, gpt2_tiny, quickstart_mlp
+from fluxmpi_b200.parallel.engine import DataParallelEngine, GraphedStep
+
+
+@pytest.fixture(scope="module", autouse=True)
+def world():
+    fm.Init()
+    yield
+    # keep the world up: other GPU test modules in this process reuse it
+
+
+def _train_reference(model, opt, batches, loss_fn):
+    losses = []
+    for x, y in batches:
+        opt.zero_grad(set_to_none=True)
+        loss = loss_fn(model(x), y)
+        loss.backward()
+        opt.step()
+        losses.append(float(loss))
+    return losses
+
+
+def _batches(n, shape, classes, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    return [(torch.randn(shape, generator=g).cuda(), torch.randint(0, classes, (shape[0],), generator=g).cuda())
+            for _ in range(n)]
+
+
+@pytest.mark.parametrize("rule,topt", [
+    (R.Adam(1e-3), lambda ps: torch.optim.Adam(ps, lr=1e-3, eps=1e-8)),
+    (R.Momentum(1e-2, 0.9), lambda ps: torch.optim.SGD(ps, lr=1e-2, momentum=0.9)),
+    (R.AdamW(1e-3, (0.9, 0.999), 1e-3 * 0.1), lambda ps: torch.optim.AdamW(ps, lr=1e-3, weight_decay=0.1)),
+])
+def test_engine_matches_torch_optim(rule, topt):
+    torch.manual_seed(0)
+    ref = resnet_tiny().cuda()
+    ours = copy.deepcopy(ref)
+    batches = _batches(5, (8, 3, 32, 32), 10)
+    loss_fn = torch.nn.functional.cross_entropy
+    ref_losses = _train_reference(ref, topt(ref.parameters()), batches, loss_fn)
+    eng = DataParallelEngine(ours, fm.DistributedOptimizer(rule))
+    assert eng.fused and eng.native
+    before = _native.launch_count
+    losses = []
+    for x, y in batches:
+        loss = loss_fn(ours(x), y)
+        loss.backward()
+        eng.step()
+        losses.append(float(loss))
+    assert _native.launch_count - before >= 2 * len(batches)      # fused step + step counter
+    assert torch.allclose(torch.tensor(losses), torch.tensor(ref_losses), rtol=2e-3, atol=2e-3), (losses, ref_losses)
+    for (n, a), (_, b) in zip(ours.named_parameters(), ref.named_parameters()):
+        assert torch.allclose(a, b, rtol=5e-3, atol=1e-3), n
+    # parameters and grads are views of the flat symmetric buffers
+    fp = eng.flat_params()
+    name, p = next(iter(ours.named_parameters()))
+    assert fp[name].data_ptr() == p.data_ptr()
+    assert float(eng.G.abs().sum()) == 0.0
+    eng.close()
+
+
+def test_engine_channels_last_and_autocast_bf16_graph():
+    """The bench configuration in miniature: channels_last, bf16 autocast, whole step in one
+    CUDA graph; compared with the eager engine step by step."""
+    torch.manual_seed(1)
+    base = resnet_tiny().cuda().to(memory_format=torch.channels_last)
+    a, b = copy.deepcopy(base), copy.deepcopy(base)
+    batches = _batches(6, (8, 3, 32, 32), 10, seed=3)
+    batches = [(x.contiguous(memory_format=torch.channels_last), y) for x, y in batches]
+    rule = R.Adam(1e-3)
+
+    def make_step(model, eng):
+        def fn(x, y):
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = torch.nn.functional.cross_entropy(model(x), y)
+            loss.backward()
+            return loss
+        return fn
+
+    # library warm-up outside the capture (cuDNN/cuBLAS handles, lazy kernel loading)
+    scratch = copy.deepcopy(base)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        torch.nn.functional.cross_entropy(scratch(batches[0][0]), batches[0][1]).backward()
+    torch.cuda.synchronize()
+    del scratch
+
+    ea = DataParallelEngine(a, rule)
+    for p in a.parameters():
+        if p.dim() == 4 and p.shape[1] > 1 and p.shape[2] > 1:
+            assert p.is_contiguous(memory_format=torch.channels_last), "memory format must survive flattening"
+    fa = make_step(a, ea)
+    eb = DataParallelEngine(b, rule)
+    g = GraphedStep(eb, make_step(b, eb), batches[0], warmup=0)
+    assert g.launches_per_replay >= 2
+    la, lb = [], []
+    for x, y in batches:
+        l = fa(x, y)
+        ea.step()
+        la.append(float(l))
+        lb.append(float(g(x, y)))
+    assert torch.allclose(torch.tensor(la), torch.tensor(lb), rtol=2e-2, atol=2e-2), (la, lb)
+    for pa, pb in zip(a.parameters(), b.parameters()):
+        assert torch.allclose(pa, pb, rtol=5e-2, atol=5e-3)
+    ea.close(); eb.close()
+
+
+def test_engine_bf16_params_with_master_weights():
+    torch.manual_seed(2)
+    model = gpt2_tiny().cuda().to(torch.bfloat16)
+    ref = copy.deepcopy(model).float()
+    eng = DataParallelEngine(model, R.Adam(1e-3))
+    assert eng.master is not None and eng.dtype == torch.bfloat16
+    opt = torch.optim.Adam(ref.parameters(), lr=1e-3, eps=1e-8)
+    g = torch.Generator().manual_seed(0)
+    for _ in range(4):
+        idx = torch.randint(0, 512, (4, 32), generator=g).cuda()
+        tgt = torch.randint(0, 512, (4, 32), generator=g).cuda()
+        loss = torch.nn.functional.cross_entropy(model(idx).float().view(-1, 512), tgt.view(-1))
+        loss.backward()
+        eng.step()
+        opt.zero_grad()
+        lr = torch.nn.functional.cross_entropy(ref(idx).view(-1, 512), tgt.view(-1))
+        lr.backward()
+        opt.step()
+    assert abs(float(loss) - float(lr)) < 0.1
+    st = eng.gather_state()
+    assert st["step"] == 4 and st["m"].shape == (eng.numel,)
+    eng.close()
+
+
+def test_engine_unfused_rule_path():
+    torch.manual_seed(3)
+    ref = quickstart_mlp().cuda()
+    ours = copy.deepcopy(ref)
+    eng = DataParallelEngine(ours, R.RMSProp(1e-3, 0.9, 1e-8))
+    assert not eng.fused
+    opt = torch.optim.RMSprop(ref.parameters(), lr=1e-3, alpha=0.9, eps=1e-8)
+    x = torch.rand(16, 1, device="cuda")
+    for _ in range(3):
+        ((ours(x) - x ** 2) ** 2).sum().backward()
+        eng.step()
+        opt.zero_grad()
+        ((ref(x) - x ** 2) ** 2).sum().backward()
+        opt.step()
+    for a, b in zip(ours.parameters(), ref.parameters()):
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-6)
+    eng.close()
+
+
+def test_functional_api_on_device_tensors():
+    """The reference-shaped calls with CUDA tensors at a world of one, plus the fused
+    multi-tensor update through rules.update_."""
+    t = torch.ones(5, device="cuda")
+    assert fm.allreduce_(t, "+") is t and torch.equal(t, torch.ones(5, device="cuda"))
+    assert fm.bcast_(t, 0) is t and fm.reduce_(t, "max", 0) is t
+    y, req = fm.Iallreduce(t, torch.zeros(5, device="cuda"), "+")
+    req.wait(sync=True)
+    assert torch.equal(y, t)
+    tree = {"a": torch.ones(3, device="cuda"), "b": (torch.zeros(2, 2, device="cuda"), None, 1.5)}
+    out = fm.synchronize(tree)
+    assert out["b"][2] == 1.5 and out["a"] is tree["a"]
+    gs = fm.allreduce_gradients({"a": torch.ones(4, device="cuda"), "b": torch.ones(4, device="cuda")})
+    assert torch.equal(gs["a"], torch.ones(4, device="cuda"))
+
+
+def test_device_loader_pinned_double_buffered():
+    xs = torch.arange(64 * 6, dtype=torch.float32).reshape(64, 6)
+    ys = torch.arange(64)
+    shard = fm.DistributedDataContainer(fm.TensorDataset(xs, ys))
+    loader = fm.DeviceLoader(shard, batch_size=8, depth=3)
+    seen = []
+    for xb, yb in loader:
+        assert xb.is_cuda and xb.shape == (8, 6)
+        assert torch.equal(xb.cpu(), xs[yb.cpu()])
+        seen += yb.tolist()
+    assert seen == list(range(64))
+    assert loader.h2d_bytes == 64 * 6 * 4 + 64 * 8
+
+
+def test_topology_is_discovered():
+    topo = fm.topology()
+    assert topo["device_count"] >= 1
+    d0 = topo["devices"][0]
+    assert d0["sm_count"] > 0 and "name" in d0 and "multicast" in d0

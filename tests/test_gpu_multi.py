@@ -1,0 +1,41 @@
+"""Real multi-GPU runs (one process per GPU) of the device collectives and the engine.
+Skipped unless the box has at least two GPUs (`gpurun --gpus N`)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+    pytest.skip("needs at least two CUDA devices", allow_module_level=True)
+
+from conftest import run_spmd
+
+NGPU = torch.cuda.device_count()
+WORLDS = sorted({2, min(4, NGPU), NGPU} & set(range(2, NGPU + 1)))
+
+
+def _run(script, w, **kw):
+    code, outs = run_spmd(script, w, timeout=600, **kw)
+    joined = "\n".join(f"--- rank {i} ---\n{o[-3000:]}" for i, o in enumerate(outs))
+    assert code == 0, joined
+    for r, o in enumerate(outs):
+        assert f"RANK_OK {r}" in o, joined
+
+
+@pytest.mark.parametrize("w", WORLDS)
+def test_device_collectives(w):
+    _run("gpu_collectives.py", w)
+
+
+@pytest.mark.parametrize("w", WORLDS)
+def test_engine_replicas_and_reference(w):
+    _run("gpu_engine.py", w)
+
+
+def test_ipc_mode_and_no_multicast():
+    _run("gpu_collectives.py", 2, env={"FMPI_SYMM_MODE": "ipc"}, args=("quick",))
+    _run("gpu_collectives.py", 2, env={"FMPI_DISABLE_MULTICAST": "1"}, args=("quick",))
+
+
+def test_nccl_fallback_when_p2p_disabled():
+    _run("gpu_collectives.py", 2, env={"FMPI_DISABLE_P2P": "1"}, args=("quick",))
