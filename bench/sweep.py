@@ -1,0 +1,122 @@
+#!/usr/bin/env python
+"""Collective bandwidth sweep — BASELINE config 5: "allreduce/bcast/reduce bandwidth sweep
+1 KB-1 GB at 2/4/8 GPUs vs ... NCCL" (the reference's CUDA-aware-MPI build cannot run here).
+
+    python -m fluxmpi_b200.launch -n 8 bench/sweep.py [--max-mb 1024] [--out gpurun_out/sweep_8.json]
+
+Every number is device time (CUDA events on the launching stream, after warm-up), max over
+ranks. Bus bandwidth conventions: allreduce busbw = bytes/time * 2(W-1)/W,
+bcast / reduce busbw = bytes/time. Between timed iterations the buffers rotate through a pool
+larger than the 126 MB L2 for small messages; large messages exceed L2 by themselves.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+from pathlib import Path
+
+import torch
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import fluxmpi_b200 as fm                                    # noqa: E402
+from fluxmpi_b200 import _native                             # noqa: E402
+
+
+def time_op(fn, bufs, iters, warm):
+    """Average device ms per call of fn(buf) cycling through bufs."""
+    for i in range(warm):
+        fn(bufs[i % len(bufs)])
+    fm.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters):
+        fn(bufs[i % len(bufs)])
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / iters
+    t = torch.tensor([ms], dtype=torch.float64)
+    fm.allreduce_(t, "max")
+    return float(t)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--max-mb", type=float, default=1024)
+    ap.add_argument("--min-bytes", type=int, default=1024)
+    ap.add_argument("--dtype", default="float32")
+    ap.add_argument("--out", default="")
+    ap.add_argument("--ops", default="allreduce,bcast,reduce")
+    ap.add_argument("--no-nccl", action="store_true")
+    a = ap.parse_args()
+
+    fm.Init()
+    r, w = fm.local_rank(), fm.total_workers()
+    dev = fm.current_device()
+    dw = fm.runtime.state().device_world
+    dt = getattr(torch, a.dtype)
+    es = torch.empty((), dtype=dt).element_size()
+
+    dist = None
+    if not a.no_nccl and w > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", rank=r, world_size=w, device_id=dev)
+
+    sizes = []
+    s = a.min_bytes
+    while s <= a.max_mb * (1 << 20):
+        sizes.append(s)
+        s *= 4
+    rows = []
+    pool_bytes = 192 << 20
+    for nbytes in sizes:
+        n = nbytes // es
+        nbuf = max(1, min(64, pool_bytes // nbytes))
+        bufs = [torch.ones(n, dtype=dt, device=dev) for _ in range(nbuf)]
+        iters = 200 if nbytes <= (1 << 20) else 40 if nbytes <= (64 << 20) else 10
+        warm = max(3, iters // 10)
+        row = {"bytes": nbytes, "world": w}
+        for op in a.ops.split(","):
+            if op == "allreduce":
+                ours = lambda b: fm.allreduce_(b, "sum")
+                nccl = (lambda b: dist.all_reduce(b)) if dist else None
+                factor = 2 * (w - 1) / w
+            elif op == "bcast":
+                ours = lambda b: fm.bcast_(b, 0)
+                nccl = (lambda b: dist.broadcast(b, 0)) if dist else None
+                factor = 1.0
+            else:
+                ours = lambda b: fm.reduce_(b, "sum", 0)
+                nccl = (lambda b: dist.reduce(b, 0)) if dist else None
+                factor = 1.0
+            ms = time_op(ours, bufs, iters, warm)
+            row[f"{op}_us"] = round(ms * 1e3, 2)
+            row[f"{op}_busbw_gbs"] = round(nbytes / (ms * 1e-3) * factor / 1e9, 2)
+            if nccl is not None:
+                for b in bufs:
+                    b.fill_(1)
+                msn = time_op(nccl, bufs, iters, warm)
+                row[f"{op}_nccl_us"] = round(msn * 1e3, 2)
+                row[f"{op}_nccl_busbw_gbs"] = round(nbytes / (msn * 1e-3) * factor / 1e9, 2)
+                row[f"{op}_speedup"] = round(msn / ms, 3)
+            for b in bufs:
+                b.fill_(1)
+        rows.append(row)
+        if r == 0:
+            print(json.dumps(row), flush=True)
+        del bufs
+        torch.cuda.empty_cache()
+    if r == 0 and a.out:
+        Path(a.out).parent.mkdir(parents=True, exist_ok=True)
+        Path(a.out).write_text(json.dumps({
+            "world": w, "dtype": a.dtype, "mode": dw.mode, "multicast": dw.has_multicast,
+            "timing": "CUDA events, max over ranks", "rows": rows}, indent=1))
+    if dist:
+        dist.destroy_process_group()
+    fm.Finalize()
+
+
+if __name__ == "__main__":
+    main()
