@@ -24,12 +24,37 @@ import fluxmpi_b200 as fm                                    # noqa: E402
 from fluxmpi_b200 import _native                             # noqa: E402
 
 
-def time_op(fn, bufs, iters, warm):
-    """Average device ms per call of fn(buf) cycling through bufs."""
+def time_op(fn, bufs, iters, warm, graph=False):
+    """Average device ms per call of fn(buf) cycling through bufs. With graph=True the calls
+    are captured into a CUDA graph first, so the number is device time free of host launch
+    overhead (the regime that matters once a training step is itself a graph)."""
     for i in range(warm):
         fn(bufs[i % len(bufs)])
     fm.barrier()
     torch.cuda.synchronize()
+    if graph:
+        inner = min(iters, 20)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.stream(side):
+            with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
+                for i in range(inner):
+                    fn(bufs[i % len(bufs)])
+        reps = max(1, iters // inner)
+        g.replay()
+        torch.cuda.synchronize()
+        fm.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / (reps * inner)
+        t = torch.tensor([ms], dtype=torch.float64)
+        fm.allreduce_(t, "max")
+        return float(t)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(iters):
@@ -50,6 +75,7 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--ops", default="allreduce,bcast,reduce")
     ap.add_argument("--no-nccl", action="store_true")
+    ap.add_argument("--graph", action="store_true", help="time CUDA-graph replays (no host launch cost)")
     a = ap.parse_args()
 
     fm.Init()
@@ -91,13 +117,13 @@ def main():
                 ours = lambda b: fm.reduce_(b, "sum", 0)
                 nccl = (lambda b: dist.reduce(b, 0)) if dist else None
                 factor = 1.0
-            ms = time_op(ours, bufs, iters, warm)
+            ms = time_op(ours, bufs, iters, warm, a.graph)
             row[f"{op}_us"] = round(ms * 1e3, 2)
             row[f"{op}_busbw_gbs"] = round(nbytes / (ms * 1e-3) * factor / 1e9, 2)
             if nccl is not None:
                 for b in bufs:
                     b.fill_(1)
-                msn = time_op(nccl, bufs, iters, warm)
+                msn = time_op(nccl, bufs, iters, warm, a.graph)
                 row[f"{op}_nccl_us"] = round(msn * 1e3, 2)
                 row[f"{op}_nccl_busbw_gbs"] = round(nbytes / (msn * 1e-3) * factor / 1e9, 2)
                 row[f"{op}_speedup"] = round(msn / ms, 3)
@@ -112,7 +138,8 @@ def main():
         Path(a.out).parent.mkdir(parents=True, exist_ok=True)
         Path(a.out).write_text(json.dumps({
             "world": w, "dtype": a.dtype, "mode": dw.mode, "multicast": dw.has_multicast,
-            "timing": "CUDA events, max over ranks", "rows": rows}, indent=1))
+            "timing": "CUDA events, max over ranks" + (", CUDA-graph replay" if a.graph else ", eager launches"),
+            "rows": rows}, indent=1))
     if dist:
         dist.destroy_process_group()
     fm.Finalize()

@@ -14,11 +14,18 @@
 //                  in rank order and stores the result into every peer's window
 //                  (dest_root >= 0: into root's only = reduce!).
 //   twoshot_stage  arbitrary user buffers: scatter-push slices into the owners' staging,
-//                  owner reduces locally, pushes the result to all peers' staging, local copy out.
+//                  owner reduces (own slice straight from its input), pushes the result to the
+//                  peers' staging and writes its own output directly, peers copy out.
 //                  All NVLink traffic is posted writes.
-//   bcast_*        root pushes (direct for small, scatter + all-gather for large so the root's
-//                  link carries N*(W-1)/W instead of N*(W-1)).
+//   nvls_*         in-switch reduction: multimem.ld_reduce pulls ONE reduced vector through the
+//                  NVSwitch instead of W peer vectors, multimem.st replicates the result to all
+//                  GPUs with one store. Link bytes per direction ~ N instead of 2N(W-1)/W.
+//   bcast_*        root pushes (direct / multicast for small, scatter + all-gather for large
+//                  P2P so the root's link carries N*(W-1)/W instead of N*(W-1)).
 // One owner per slice + fixed rank order 0..W-1 => every rank ends with bit-identical data.
+//
+// Memory-level parallelism: every loop loads a batch of U vectors before it touches any of
+// them (the asm loads are volatile, so the batch is what puts requests in flight).
 #include <cstdarg>
 #include <cstdio>
 #include <string>
@@ -51,29 +58,65 @@ struct PtrTable {
   void* p[FMPI_MAX_RANKS];
 };
 
-// Reduce one 16-byte vector of W buffers in rank order. `addr(r)` yields rank r's address;
-// with the loops fully unrolled r is a compile-time constant, so peer base pointers come
-// straight from the kernel-parameter bank (no pointer arrays on the stack).
-template <typename T, bool kPeerWrittenLocal, typename AddrFn>
-__device__ __forceinline__ uint4 reduce_vec(AddrFn addr, int world, int op) {
-  using V = VecOps<T>;
-  uint4 raw[FMPI_MAX_RANKS];
+__host__ __device__ inline uint64_t ceil_div(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
+
+// Vectors j in [lo, hi) with j == lo + t0 (mod stride) belong to this thread; U are in flight.
+// The block -> vector mapping does not depend on U, so producer and consumer phases that use
+// this helper with the same (lo, t0, stride) meet on the same block (= the same barrier).
+template <int U, typename LoadFn, typename StoreFn>
+__device__ __forceinline__ void vec_loop(uint64_t lo, uint64_t hi, uint64_t t0, uint64_t stride,
+                                         LoadFn ld, StoreFn st) {
+  for (uint64_t i = lo + t0; i < hi; i += U * stride) {
+    uint4 v[U];
 #pragma unroll
-  for (int r = 0; r < FMPI_MAX_RANKS; ++r)
-    if (r < world) raw[r] = kPeerWrittenLocal ? ld_volatile(addr(r)) : ld_stream(addr(r));
-  typename V::Acc acc[V::kN], b[V::kN];
-  V::unpack(raw[0], acc);
+    for (int k = 0; k < U; ++k)
+      if (i + k * stride < hi) v[k] = ld(i + k * stride);
 #pragma unroll
-  for (int r = 1; r < FMPI_MAX_RANKS; ++r)
-    if (r < world) {
-      V::unpack(raw[r], b);
-#pragma unroll
-      for (int k = 0; k < V::kN; ++k) acc[k] = op_apply(acc[k], b[k], op);
-    }
-  return V::pack(acc);
+    for (int k = 0; k < U; ++k)
+      if (i + k * stride < hi) st(i + k * stride, v[k]);
+  }
 }
 
-__host__ __device__ inline uint64_t ceil_div(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
+// Same, but each element is the rank-ordered reduction of W vectors; addr(r, j) yields rank r's
+// copy of vector j. All U*W loads are issued before any arithmetic.
+template <typename T, int U, bool kPeerWritten, typename AddrFn, typename StoreFn>
+__device__ __forceinline__ void reduce_loop(uint64_t lo, uint64_t hi, uint64_t t0, uint64_t stride,
+                                            int world, int op, AddrFn addr, StoreFn st) {
+  using V = VecOps<T>;
+  for (uint64_t i = lo + t0; i < hi; i += U * stride) {
+    uint4 raw[U][FMPI_MAX_RANKS];
+#pragma unroll
+    for (int k = 0; k < U; ++k)
+      if (i + k * stride < hi) {
+#pragma unroll
+        for (int r = 0; r < FMPI_MAX_RANKS; ++r)
+          if (r < world)
+            raw[k][r] = kPeerWritten ? ld_volatile(addr(r, i + k * stride)) : ld_stream(addr(r, i + k * stride));
+      }
+#pragma unroll
+    for (int k = 0; k < U; ++k)
+      if (i + k * stride < hi) {
+        typename V::Acc acc[V::kN], b[V::kN];
+        V::unpack(raw[k][0], acc);
+#pragma unroll
+        for (int r = 1; r < FMPI_MAX_RANKS; ++r)
+          if (r < world) {
+            V::unpack(raw[k][r], b);
+#pragma unroll
+            for (int e = 0; e < V::kN; ++e) acc[e] = op_apply(acc[e], b[e], op);
+          }
+        st(i + k * stride, V::pack(acc));
+      }
+  }
+}
+
+template <typename Fn>
+__device__ __forceinline__ void store_to_ranks(const fmpi_devcomm& c, int dest_root, int skip, Fn ptr_of,
+                                               uint4 v) {
+#pragma unroll
+  for (int r = 0; r < FMPI_MAX_RANKS; ++r)
+    if (r < c.world && r != skip && (dest_root < 0 || r == dest_root)) st_stream(ptr_of(r), v);
+}
 
 // ---------------------------------------------------------------------------- barrier
 __global__ void barrier_kernel(fmpi_devcomm c) {
@@ -102,36 +145,28 @@ oneshot_push_kernel(fmpi_devcomm c, PtrTable in, PtrTable out, uint64_t nbytes, 
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
   const uint64_t t0 = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
 
-  // push
-  for (uint64_t i = t0; i < nvec; i += stride) {
-    const uint4 v = ld_stream(src + i * 16);
-#pragma unroll
-    for (int r = 0; r < FMPI_MAX_RANKS; ++r)
-      if (r < c.world && (dest_root < 0 || r == dest_root))
-        st_stream(byte_ptr(c.data[r], my_slot) + i * 16, v);
-  }
+  vec_loop<2>(0, nvec, t0, stride, [&](uint64_t j) { return ld_stream(src + j * 16); },
+              [&](uint64_t j, uint4 v) {
+                store_to_ranks(c, dest_root, -1, [&](int r) { return byte_ptr(c.data[r], my_slot) + j * 16; }, v);
+              });
   if (tail && t0 == 0) {  // last partial vector: zero-padded
     uint4 v = make_uint4(0, 0, 0, 0);
     uint8_t* vb = reinterpret_cast<uint8_t*>(&v);
     for (uint64_t k = 0; k < tail; ++k) vb[k] = src[nvec * 16 + k];
-#pragma unroll
-    for (int r = 0; r < FMPI_MAX_RANKS; ++r)
-      if (r < c.world && (dest_root < 0 || r == dest_root))
-        st_stream(byte_ptr(c.data[r], my_slot) + nvec * 16, v);
+    store_to_ranks(c, dest_root, -1, [&](int r) { return byte_ptr(c.data[r], my_slot) + nvec * 16; }, v);
   }
   block_barrier(x, c);
 
-  // reduce my W slots (local memory that peers wrote)
   if (dest_root < 0 || x.rank == dest_root) {
     const uint8_t* base = byte_ptr(c.data[x.rank], stage_off + parity * c.world * slot_bytes);
-    for (uint64_t i = t0; i < nvec; i += stride)
-      *reinterpret_cast<uint4*>(dst + i * 16) = reduce_vec<T, true>(
-          [&](int r) { return base + uint64_t(r) * slot_bytes + i * 16; }, c.world, op);
+    auto addr = [&](int r, uint64_t j) { return base + uint64_t(r) * slot_bytes + j * 16; };
+    reduce_loop<T, 1, true>(0, nvec, t0, stride, c.world, op, addr,
+                            [&](uint64_t j, uint4 v) { *reinterpret_cast<uint4*>(dst + j * 16) = v; });
     if (tail && t0 == 0) {
-      const uint4 v = reduce_vec<T, true>(
-          [&](int r) { return base + uint64_t(r) * slot_bytes + nvec * 16; }, c.world, op);
-      const uint8_t* vb = reinterpret_cast<const uint8_t*>(&v);
-      for (uint64_t k = 0; k < tail; ++k) dst[nvec * 16 + k] = vb[k];
+      reduce_loop<T, 1, true>(nvec, nvec + 1, 0, 1, c.world, op, addr, [&](uint64_t, uint4 v) {
+        const uint8_t* vb = reinterpret_cast<const uint8_t*>(&v);
+        for (uint64_t k = 0; k < tail; ++k) dst[nvec * 16 + k] = vb[k];
+      });
     }
   }
   seq_advance(x, seq);
@@ -149,15 +184,34 @@ twoshot_symm_kernel(fmpi_devcomm c, uint64_t off, uint64_t nvec, int op, int des
   const uint64_t per = ceil_div(nvec, c.world);
   const uint64_t lo = min(per * x.rank, nvec), hi = min(lo + per, nvec);
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
-  for (uint64_t i = lo + uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += stride) {
-    const uint4 v = reduce_vec<T, false>(
-        [&](int r) { return byte_ptr(c.data[r], off) + i * 16; }, c.world, op);
-#pragma unroll
-    for (int r = 0; r < FMPI_MAX_RANKS; ++r)
-      if (r < c.world && (dest_root < 0 || r == dest_root))
-        st_stream(byte_ptr(c.data[r], off) + i * 16, v);
-  }
+  const uint64_t t0 = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  reduce_loop<T, 2, false>(
+      lo, hi, t0, stride, c.world, op, [&](int r, uint64_t j) { return byte_ptr(c.data[r], off) + j * 16; },
+      [&](uint64_t j, uint4 v) {
+        store_to_ranks(c, dest_root, -1, [&](int r) { return byte_ptr(c.data[r], off) + j * 16; }, v);
+      });
   block_barrier(x, c);  // all results have landed everywhere
+  ctx_finish(x);
+}
+
+// In-switch version (sum of f32 / f16 / bf16): one multimem.ld_reduce + one multimem.st per vector.
+template <typename T>
+__global__ void __launch_bounds__(512)
+nvls_symm_kernel(fmpi_devcomm c, uint64_t off, uint64_t nvec, int dest_root) {
+  Ctx x;
+  ctx_init(x, c);
+  block_barrier(x, c);
+  const uint64_t per = ceil_div(nvec, c.world);
+  const uint64_t lo = min(per * x.rank, nvec), hi = min(lo + per, nvec);
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  const uint64_t t0 = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  uint8_t* mc = byte_ptr(c.mc_data, off);
+  vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return Multimem<T>::ld_reduce(mc + j * 16); },
+              [&](uint64_t j, uint4 v) {
+                if (dest_root < 0) multimem_st(mc + j * 16, v);
+                else st_stream(byte_ptr(c.data[dest_root], off) + j * 16, v);
+              });
+  block_barrier(x, c);
   ctx_finish(x);
 }
 
@@ -179,82 +233,138 @@ twoshot_stage_kernel(fmpi_devcomm c, PtrTable in, PtrTable out, uint64_t nvec, i
   const uint64_t t0 = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
 
   // phase A: scatter-push slice q of my input into owner q's staging slot [my rank]
-  for (int q = 0; q < c.world; ++q) {
+  // (my own slice stays where it is: phase B reads it straight from the input)
+  for (int dq = 1; dq < c.world; ++dq) {
+    const int q = (x.rank + dq) % c.world;  // staggered so the ranks do not gang up on one peer
     const uint64_t lo = min(per * q, nvec), hi = min(lo + per, nvec);
     uint8_t* slot = byte_ptr(c.data[q], stage_off + uint64_t(x.rank) * scatter_bytes);
-    for (uint64_t i = lo + t0; i < hi; i += stride)
-      st_stream(slot + (i - lo) * 16, ld_stream(src + i * 16));
+    vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_stream(src + j * 16); },
+                [&](uint64_t j, uint4 v) { st_stream(slot + (j - lo) * 16, v); });
   }
   block_barrier(x, c);
 
-  // phase B: reduce my slice from local slots, push the result to every rank's result area
+  // phase B: reduce my slice, push the result to the peers' result areas, write mine directly
   {
     const uint64_t lo = min(per * x.rank, nvec), hi = min(lo + per, nvec);
     const uint8_t* base = byte_ptr(c.data[x.rank], stage_off);
-    for (uint64_t i = lo + t0; i < hi; i += stride) {
-      const uint4 v = reduce_vec<T, true>(
-          [&](int r) { return base + uint64_t(r) * scatter_bytes + (i - lo) * 16; }, c.world, op);
-#pragma unroll
-      for (int r = 0; r < FMPI_MAX_RANKS; ++r)
-        if (r < c.world && (dest_root < 0 || r == dest_root))
-          st_stream(byte_ptr(c.data[r], result_off) + i * 16, v);
-    }
+    const int me = x.rank;
+    const bool mine_too = dest_root < 0 || dest_root == me;
+    reduce_loop<T, 2, true>(
+        lo, hi, t0, stride, c.world, op,
+        [&](int r, uint64_t j) { return r == me ? src + j * 16 : base + uint64_t(r) * scatter_bytes + (j - lo) * 16; },
+        [&](uint64_t j, uint4 v) {
+          store_to_ranks(c, dest_root, me, [&](int r) { return byte_ptr(c.data[r], result_off) + j * 16; }, v);
+          if (mine_too) *reinterpret_cast<uint4*>(dst + j * 16) = v;
+        });
   }
   block_barrier(x, c);
 
-  // phase C: local copy out (same block -> element mapping as the writers used)
+  // phase C: copy the other owners' slices out of my result area
   if (dest_root < 0 || x.rank == dest_root) {
     const uint8_t* res = byte_ptr(c.data[x.rank], result_off);
+    for (int dq = 1; dq < c.world; ++dq) {
+      const int q = (x.rank + dq) % c.world;
+      const uint64_t lo = min(per * q, nvec), hi = min(lo + per, nvec);
+      vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_volatile(res + j * 16); },
+                  [&](uint64_t j, uint4 v) { *reinterpret_cast<uint4*>(dst + j * 16) = v; });
+    }
+  }
+  ctx_finish(x);
+}
+
+// In-switch version for arbitrary buffers: copy in -> ld_reduce/st on the multicast alias of the
+// staging area (in place: only the owner ever touches a vector) -> copy out.
+template <typename T>
+__global__ void __launch_bounds__(512)
+nvls_stage_kernel(fmpi_devcomm c, PtrTable in, PtrTable out, uint64_t nvec, uint64_t stage_off,
+                  int dest_root) {
+  Ctx x;
+  ctx_init(x, c);
+  const int ai = arg_index(c);
+  const uint8_t* src = static_cast<const uint8_t*>(in.p[ai]);
+  uint8_t* dst = static_cast<uint8_t*>(out.p[ai]);
+  const uint64_t per = ceil_div(nvec, c.world);
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  const uint64_t t0 = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  uint8_t* mine = byte_ptr(c.data[x.rank], stage_off);
+  uint8_t* mc = byte_ptr(c.mc_data, stage_off);
+
+  for (int q = 0; q < c.world; ++q) {  // slice-wise so every phase maps vectors to the same block
+    const uint64_t lo = min(per * q, nvec), hi = min(lo + per, nvec);
+    vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_stream(src + j * 16); },
+                [&](uint64_t j, uint4 v) { st_stream(mine + j * 16, v); });
+  }
+  block_barrier(x, c);
+  {
+    const uint64_t lo = min(per * x.rank, nvec), hi = min(lo + per, nvec);
+    vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return Multimem<T>::ld_reduce(mc + j * 16); },
+                [&](uint64_t j, uint4 v) {
+                  if (dest_root < 0) multimem_st(mc + j * 16, v);
+                  else st_stream(byte_ptr(c.data[dest_root], stage_off) + j * 16, v);
+                });
+  }
+  block_barrier(x, c);
+  if (dest_root < 0 || x.rank == dest_root) {
     for (int q = 0; q < c.world; ++q) {
       const uint64_t lo = min(per * q, nvec), hi = min(lo + per, nvec);
-      for (uint64_t i = lo + t0; i < hi; i += stride)
-        *reinterpret_cast<uint4*>(dst + i * 16) = ld_volatile(res + i * 16);
+      vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_volatile(mine + j * 16); },
+                  [&](uint64_t j, uint4 v) { *reinterpret_cast<uint4*>(dst + j * 16) = v; });
     }
   }
   ctx_finish(x);
 }
 
 // ---------------------------------------------------------------------------- broadcast
-// Symmetric, in place: direct (root stores to all) or scatter + all-gather.
+// Symmetric, in place. mode 0: root stores to every peer; 1: scatter + all-gather; 2: multicast.
 __global__ void __launch_bounds__(512)
-bcast_symm_kernel(fmpi_devcomm c, uint64_t off, uint64_t nvec, int root, int sag) {
+bcast_symm_kernel(fmpi_devcomm c, uint64_t off, uint64_t nvec, int root, int mode) {
   Ctx x;
   ctx_init(x, c);
   block_barrier(x, c);  // peers are done with whatever used this region before
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
   const uint64_t t0 = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (!sag) {
+  const uint8_t* src = byte_ptr(c.data[x.rank], off);
+  if (mode != 1) {
     if (x.rank == root) {
-      const uint8_t* src = byte_ptr(c.data[root], off);
-      for (uint64_t i = t0; i < nvec; i += stride) {
-        const uint4 v = ld_stream(src + i * 16);
-#pragma unroll
-        for (int r = 0; r < FMPI_MAX_RANKS; ++r)
-          if (r < c.world && r != root) st_stream(byte_ptr(c.data[r], off) + i * 16, v);
+      if (mode == 2) {
+        uint8_t* mc = byte_ptr(c.mc_data, off);
+        vec_loop<4>(0, nvec, t0, stride, [&](uint64_t j) { return ld_stream(src + j * 16); },
+                    [&](uint64_t j, uint4 v) { multimem_st(mc + j * 16, v); });
+      } else {
+        vec_loop<4>(0, nvec, t0, stride, [&](uint64_t j) { return ld_stream(src + j * 16); },
+                    [&](uint64_t j, uint4 v) {
+                      store_to_ranks(c, -1, root, [&](int r) { return byte_ptr(c.data[r], off) + j * 16; }, v);
+                    });
       }
     }
     block_barrier(x, c);
   } else {
     const uint64_t per = ceil_div(nvec, c.world);
-    if (x.rank == root) {  // scatter: slice q -> rank q
-      const uint8_t* src = byte_ptr(c.data[root], off);
-      for (int q = 0; q < c.world; ++q) {
-        if (q == root) continue;
+    if (x.rank == root) {
+      for (int dq = 1; dq < c.world; ++dq) {  // scatter: slice q -> rank q
+        const int q = (root + dq) % c.world;
         const uint64_t lo = min(per * q, nvec), hi = min(lo + per, nvec);
         uint8_t* d = byte_ptr(c.data[q], off);
-        for (uint64_t i = lo + t0; i < hi; i += stride) st_stream(d + i * 16, ld_stream(src + i * 16));
+        vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_stream(src + j * 16); },
+                    [&](uint64_t j, uint4 v) { st_stream(d + j * 16, v); });
       }
+      // the root owns its slice: it goes to everybody directly
+      const uint64_t lo = min(per * root, nvec), hi = min(lo + per, nvec);
+      vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_stream(src + j * 16); },
+                  [&](uint64_t j, uint4 v) {
+                    store_to_ranks(c, -1, root, [&](int r) { return byte_ptr(c.data[r], off) + j * 16; }, v);
+                  });
     }
     block_barrier(x, c);
     if (x.rank != root) {  // all-gather: my slice -> everyone except root and me
       const uint64_t lo = min(per * x.rank, nvec), hi = min(lo + per, nvec);
-      const uint8_t* src = byte_ptr(c.data[x.rank], off);
-      for (uint64_t i = lo + t0; i < hi; i += stride) {
-        const uint4 v = ld_volatile(src + i * 16);
+      const int me = x.rank;
+      vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_volatile(src + j * 16); },
+                  [&](uint64_t j, uint4 v) {
 #pragma unroll
-        for (int r = 0; r < FMPI_MAX_RANKS; ++r)
-          if (r < c.world && r != root && r != x.rank) st_stream(byte_ptr(c.data[r], off) + i * 16, v);
-      }
+                    for (int r = 0; r < FMPI_MAX_RANKS; ++r)
+                      if (r < c.world && r != root && r != me) st_stream(byte_ptr(c.data[r], off) + j * 16, v);
+                  });
     }
     block_barrier(x, c);
   }
@@ -264,7 +374,7 @@ bcast_symm_kernel(fmpi_devcomm c, uint64_t off, uint64_t nvec, int root, int sag
 // Arbitrary buffers through double-buffered staging: [parity][nbytes rounded to 16].
 __global__ void __launch_bounds__(512)
 bcast_stage_kernel(fmpi_devcomm c, PtrTable buf, uint64_t nbytes, int root, uint64_t stage_off,
-                   uint64_t half_bytes, int sag) {
+                   uint64_t half_bytes, int mode) {
   Ctx x;
   ctx_init(x, c);
   const int ai = arg_index(c);
@@ -276,84 +386,76 @@ bcast_stage_kernel(fmpi_devcomm c, PtrTable buf, uint64_t nbytes, int root, uint
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
   const uint64_t t0 = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
   const uint64_t per = ceil_div(nv, c.world);
+  const int me = x.rank;
 
-  auto load_user = [&](uint64_t i) -> uint4 {
-    if (i < nvec) return ld_stream(user + i * 16);
+  auto load_user = [&](uint64_t j) -> uint4 {
+    if (j < nvec) return ld_stream(user + j * 16);
     uint4 v = make_uint4(0, 0, 0, 0);
     uint8_t* vb = reinterpret_cast<uint8_t*>(&v);
     for (uint64_t k = 0; k < tail; ++k) vb[k] = user[nvec * 16 + k];
     return v;
   };
-
-  if (x.rank == root) {
-    if (!sag) {
-      for (uint64_t i = t0; i < nv; i += stride) {
-        const uint4 v = load_user(i);
-#pragma unroll
-        for (int r = 0; r < FMPI_MAX_RANKS; ++r)
-          if (r < c.world && r != root) st_stream(byte_ptr(c.data[r], base) + i * 16, v);
-      }
+  auto store_user = [&](uint64_t j, uint4 v) {
+    if (j < nvec) {
+      *reinterpret_cast<uint4*>(user + j * 16) = v;
     } else {
-      for (int q = 0; q < c.world; ++q) {
-        if (q == root) continue;
+      const uint8_t* vb = reinterpret_cast<const uint8_t*>(&v);
+      for (uint64_t k = 0; k < tail; ++k) user[nvec * 16 + k] = vb[k];
+    }
+  };
+  auto to_all_but_root = [&](uint64_t j, uint4 v) {
+    store_to_ranks(c, -1, root, [&](int r) { return byte_ptr(c.data[r], base) + j * 16; }, v);
+  };
+
+  if (me == root) {
+    if (mode == 2) {
+      uint8_t* mc = byte_ptr(c.mc_data, base);
+      vec_loop<4>(0, nv, t0, stride, load_user, [&](uint64_t j, uint4 v) { multimem_st(mc + j * 16, v); });
+    } else if (mode == 0) {
+      vec_loop<4>(0, nv, t0, stride, load_user, to_all_but_root);
+    } else {
+      for (int dq = 1; dq < c.world; ++dq) {
+        const int q = (root + dq) % c.world;
         const uint64_t lo = min(per * q, nv), hi = min(lo + per, nv);
-        for (uint64_t i = lo + t0; i < hi; i += stride)
-          st_stream(byte_ptr(c.data[q], base) + i * 16, load_user(i));
+        uint8_t* d = byte_ptr(c.data[q], base);
+        vec_loop<4>(lo, hi, t0, stride, load_user, [&](uint64_t j, uint4 v) { st_stream(d + j * 16, v); });
       }
-      // root's own slice goes to everyone directly (root is its owner)
       const uint64_t lo = min(per * root, nv), hi = min(lo + per, nv);
-      for (uint64_t i = lo + t0; i < hi; i += stride) {
-        const uint4 v = load_user(i);
-#pragma unroll
-        for (int r = 0; r < FMPI_MAX_RANKS; ++r)
-          if (r < c.world && r != root) st_stream(byte_ptr(c.data[r], base) + i * 16, v);
-      }
+      vec_loop<4>(lo, hi, t0, stride, load_user, to_all_but_root);
     }
   }
   block_barrier(x, c);
-  if (sag) {
-    if (x.rank != root) {
-      const uint64_t lo = min(per * x.rank, nv), hi = min(lo + per, nv);
-      const uint8_t* mine = byte_ptr(c.data[x.rank], base);
-      for (uint64_t i = lo + t0; i < hi; i += stride) {
-        const uint4 v = ld_volatile(mine + i * 16);
+  const uint8_t* mine = byte_ptr(c.data[me], base);
+  if (mode == 1) {
+    if (me != root) {
+      const uint64_t lo = min(per * me, nv), hi = min(lo + per, nv);
+      vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_volatile(mine + j * 16); },
+                  [&](uint64_t j, uint4 v) {
 #pragma unroll
-        for (int r = 0; r < FMPI_MAX_RANKS; ++r)
-          if (r < c.world && r != root && r != x.rank) st_stream(byte_ptr(c.data[r], base) + i * 16, v);
-      }
+                    for (int r = 0; r < FMPI_MAX_RANKS; ++r)
+                      if (r < c.world && r != root && r != me) st_stream(byte_ptr(c.data[r], base) + j * 16, v);
+                  });
     }
     block_barrier(x, c);
   }
-  if (x.rank != root) {
-    const uint8_t* mine = byte_ptr(c.data[x.rank], base);
-    // same block->element mapping as the writers: iterate slice by slice in sag mode
-    if (!sag) {
-      for (uint64_t i = t0; i < nv; i += stride) {
-        const uint4 v = ld_volatile(mine + i * 16);
-        if (i < nvec) {
-          *reinterpret_cast<uint4*>(user + i * 16) = v;
-        } else {
-          const uint8_t* vb = reinterpret_cast<const uint8_t*>(&v);
-          for (uint64_t k = 0; k < tail; ++k) user[nvec * 16 + k] = vb[k];
-        }
-      }
-    } else {
+  if (me != root) {
+    if (mode != 1) {
+      vec_loop<4>(0, nv, t0, stride, [&](uint64_t j) { return ld_volatile(mine + j * 16); }, store_user);
+    } else {  // slice-wise: same block -> vector mapping as the writers
       for (int q = 0; q < c.world; ++q) {
         const uint64_t lo = min(per * q, nv), hi = min(lo + per, nv);
-        for (uint64_t i = lo + t0; i < hi; i += stride) {
-          const uint4 v = ld_volatile(mine + i * 16);
-          if (i < nvec) {
-            *reinterpret_cast<uint4*>(user + i * 16) = v;
-          } else {
-            const uint8_t* vb = reinterpret_cast<const uint8_t*>(&v);
-            for (uint64_t k = 0; k < tail; ++k) user[nvec * 16 + k] = vb[k];
-          }
-        }
+        vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_volatile(mine + j * 16); }, store_user);
       }
     }
   }
   seq_advance(x, seq);
   ctx_finish(x);
+}
+
+__global__ void flush_l2_kernel(uint4* p, uint64_t nvec, uint32_t salt) {
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride)
+    p[i] = make_uint4(salt, uint32_t(i), salt ^ uint32_t(i), 0);
 }
 
 }  // namespace fmpi
@@ -379,7 +481,7 @@ int validate(const fmpi_devcomm* c) {
 struct Shape { int blocks, threads; };
 
 // Defaults: latency-bound messages want few CTAs (one barrier each), bandwidth-bound ones want
-// enough 16-byte requests in flight to cover the NVLink round trip (~1 MB per direction).
+// a CTA per SM so that enough 16-byte requests are in flight to cover HBM and NVLink latency.
 Shape pick_shape(const fmpi_devcomm* c, const fmpi_launch* l, uint64_t nbytes) {
   Shape s;
   s.threads = (l && l->threads > 0 && l->threads <= 512) ? l->threads : 512;
@@ -388,7 +490,7 @@ Shape pick_shape(const fmpi_devcomm* c, const fmpi_launch* l, uint64_t nbytes) {
   } else {
     const uint64_t per_block = uint64_t(s.threads) * 16 * 4;
     uint64_t b = (nbytes + per_block - 1) / per_block;
-    const uint64_t cap = nbytes >= (uint64_t(8) << 20) ? 64 : nbytes >= (uint64_t(1) << 20) ? 32 : 16;
+    const uint64_t cap = nbytes >= (uint64_t(4) << 20) ? 148 : nbytes >= (uint64_t(1) << 20) ? 64 : 24;
     s.blocks = int(b < 1 ? 1 : b > cap ? cap : b);
   }
   int cap = FMPI_MAX_BLOCKS;
@@ -405,6 +507,18 @@ PtrTable table(const void* const* p, const fmpi_devcomm* c) {
   return t;
 }
 
+bool nvls_capable(const fmpi_devcomm* c, int dtype, int op) {
+  return c->mc_data && !c->emulate && c->world > 1 && op == FMPI_SUM &&
+         (dtype == FMPI_F32 || dtype == FMPI_BF16 || dtype == FMPI_F16);
+}
+
+// AUTO picks the in-switch path where it moves fewer bytes per link (W >= 4) and the message
+// is past the latency regime; the Python tuner can override either way.
+bool want_nvls(const fmpi_devcomm* c, int algo, int dtype, int op, uint64_t nbytes) {
+  if (algo == FMPI_ALGO_NVLS) return true;
+  return algo == FMPI_ALGO_AUTO && nvls_capable(c, dtype, op) && c->world >= 4 && nbytes >= (512u << 10);
+}
+
 #define FMPI_DISPATCH_DTYPE(dt, EXPR)                                   \
   switch (dt) {                                                         \
     case FMPI_F32: { using T = float; EXPR; } break;                    \
@@ -419,6 +533,14 @@ PtrTable table(const void* const* p, const fmpi_devcomm* c) {
     default: rc = set_error("unsupported dtype %d", dt);                \
   }
 
+#define FMPI_DISPATCH_NVLS(dt, EXPR)                                    \
+  switch (dt) {                                                         \
+    case FMPI_F32: { using T = float; EXPR; } break;                    \
+    case FMPI_F16: { using T = __half; EXPR; } break;                   \
+    case FMPI_BF16: { using T = __nv_bfloat16; EXPR; } break;           \
+    default: rc = set_error("NVLS supports f32 / f16 / bf16 sums, got dtype %d", dt); \
+  }
+
 int reduce_symm_impl(const fmpi_devcomm* c, uint64_t off, uint64_t count, int dtype, int op,
                      int dest_root, const fmpi_launch* l, cudaStream_t st) {
   if (validate(c)) return 1;
@@ -431,6 +553,12 @@ int reduce_symm_impl(const fmpi_devcomm* c, uint64_t off, uint64_t count, int dt
   if (count == 0) return 0;
   const Shape s = pick_shape(c, l, nbytes / c->world);
   int rc = 0;
+  if (want_nvls(c, l ? l->algo : FMPI_ALGO_AUTO, dtype, op, nbytes)) {
+    if (!nvls_capable(c, dtype, op)) return set_error("NVLS requested but not possible for this call");
+    FMPI_DISPATCH_NVLS(dtype, rc = launch_ranked(nvls_symm_kernel<T>, *c, s.blocks, s.threads, st, *c,
+                                                 off, nvec, dest_root));
+    return rc;
+  }
   FMPI_DISPATCH_DTYPE(dtype, rc = launch_ranked(twoshot_symm_kernel<T>, *c, s.blocks, s.threads,
                                                 st, *c, off, nvec, op, dest_root));
   return rc;
@@ -448,9 +576,10 @@ int reduce_any_impl(const fmpi_devcomm* c, const void* const* in, void* const* o
   if (count == 0) return 0;
   const uint64_t nbytes = count * es;
   const int algo = l ? l->algo : FMPI_ALGO_AUTO;
-  // The staging area is split into two private halves so that the push-without-handshake
-  // one-shot kernel can never overwrite bytes a peer is still copying out of a two-shot call:
+  // The staging area is split into private parts so that the push-without-handshake one-shot
+  // kernel can never overwrite bytes a peer is still copying out of a two-shot call:
   //   [one-shot: 2 parities x W slots][two-shot: scatter W x per | result W x per]
+  // (the NVLS kernel uses the two-shot part; both start with a barrier-protected phase).
   uint64_t os_bytes = 2ull * c->world * ((256ull << 10) + 16);
   if (os_bytes > stage_bytes / 4) os_bytes = stage_bytes / 4;
   os_bytes &= ~uint64_t(15);
@@ -458,8 +587,9 @@ int reduce_any_impl(const fmpi_devcomm* c, const void* const* in, void* const* o
   const bool want_oneshot =
       algo == FMPI_ALGO_ONESHOT || (algo == FMPI_ALGO_AUTO && nbytes <= (256u << 10));
   const bool aligned = nbytes % 16 == 0;
+  const int n_ranks = c->emulate ? c->world : 1;
   int rc = 0;
-  for (int i = 0; i < (c->emulate ? c->world : 1); ++i)
+  for (int i = 0; i < n_ranks; ++i)
     if ((reinterpret_cast<uintptr_t>(in[i]) % 16) || (reinterpret_cast<uintptr_t>(out[i]) % 16))
       return set_error("collective buffers must be 16-byte aligned");
   if ((want_oneshot || !aligned) && nbytes + 16 <= slot) {
@@ -473,14 +603,19 @@ int reduce_any_impl(const fmpi_devcomm* c, const void* const* in, void* const* o
   if (!aligned)
     return set_error("two-shot path needs a multiple of 16 bytes (got %llu); split off the tail",
                      (unsigned long long)nbytes);
-  // two-shot staged, chunked so that scatter (N) + result (N) fit its half of the staging area.
   const uint64_t ts_off = stage_off + os_bytes, ts_bytes = stage_bytes - os_bytes;
-  uint64_t max_vec = ts_bytes / 32;                            // 2 areas x 16 B
+  const bool nvls = want_nvls(c, algo, dtype, op, nbytes);
+  if (nvls && !nvls_capable(c, dtype, op)) return set_error("NVLS requested but not possible for this call");
+  // Chunked so that a chunk fits: P2P uses scatter (N, first half) + result (N, second half).
+  // NVLS needs only N and lives in the SECOND half: a P2P call's unsynchronised scatter pushes
+  // go to the first half, so they can never hit bytes a peer is still copying out of an
+  // earlier NVLS call.
+  const uint64_t nvls_off = ts_off + ((ts_bytes / 2) & ~uint64_t(15));
+  uint64_t max_vec = ts_bytes / 32;
   max_vec = max_vec / c->world * c->world;
   if (max_vec < 2ull * c->world) return set_error("staging area too small");
-  max_vec -= c->world;                                         // room for the per-slice round-up
+  max_vec -= c->world;  // room for the per-slice round-up
   const uint64_t nvec = nbytes / 16;
-  const int n_ranks = c->emulate ? c->world : 1;
   for (uint64_t done = 0; done < nvec && rc == 0; done += max_vec) {
     const uint64_t n = nvec - done < max_vec ? nvec - done : max_vec;
     PtrTable ti{}, to{};
@@ -489,10 +624,25 @@ int reduce_any_impl(const fmpi_devcomm* c, const void* const* in, void* const* o
       to.p[i] = static_cast<uint8_t*>(out[i]) + done * 16;
     }
     const Shape s = pick_shape(c, l, n * 16);
-    FMPI_DISPATCH_DTYPE(dtype, rc = launch_ranked(twoshot_stage_kernel<T>, *c, s.blocks, s.threads,
-                                                  st, *c, ti, to, n, op, ts_off, dest_root));
+    if (nvls) {
+      FMPI_DISPATCH_NVLS(dtype, rc = launch_ranked(nvls_stage_kernel<T>, *c, s.blocks, s.threads, st, *c,
+                                                   ti, to, n, nvls_off, dest_root));
+    } else {
+      FMPI_DISPATCH_DTYPE(dtype, rc = launch_ranked(twoshot_stage_kernel<T>, *c, s.blocks, s.threads,
+                                                    st, *c, ti, to, n, op, ts_off, dest_root));
+    }
   }
   return rc;
+}
+
+// 0 direct, 1 scatter + all-gather, 2 multicast
+int bcast_mode(const fmpi_devcomm* c, int algo, uint64_t nbytes) {
+  const bool mc = c->mc_data && !c->emulate;
+  if (algo == FMPI_ALGO_NVLS) return mc ? 2 : -1;
+  if (algo == FMPI_ALGO_ONESHOT) return 0;
+  if (algo == FMPI_ALGO_TWOSHOT) return c->world > 2 ? 1 : 0;
+  if (mc && c->world > 2) return 2;
+  return (nbytes >= (1u << 20) && c->world > 2) ? 1 : 0;
 }
 
 }  // namespace
@@ -538,12 +688,11 @@ int fmpi_bcast_symm(const fmpi_devcomm* c, uint64_t off, uint64_t nbytes, int ro
   const uint64_t nvec = (nbytes + 15) / 16;
   if (off + nvec * 16 > c->data_bytes) return set_error("region exceeds the symmetric window");
   if (nbytes == 0) return 0;
-  const int algo = l ? l->algo : FMPI_ALGO_AUTO;
-  const int sag = (algo == FMPI_ALGO_TWOSHOT || (algo == FMPI_ALGO_AUTO && nbytes >= (1u << 20))) &&
-                  c->world > 2;
+  const int mode = bcast_mode(c, l ? l->algo : FMPI_ALGO_AUTO, nbytes);
+  if (mode < 0) return set_error("multicast broadcast requested but no multicast mapping");
   const Shape s = pick_shape(c, l, nbytes);
   return launch_ranked(bcast_symm_kernel, *c, s.blocks, s.threads, static_cast<cudaStream_t>(st),
-                       *c, off, nvec, root, sag);
+                       *c, off, nvec, root, mode);
 }
 
 int fmpi_bcast_any(const fmpi_devcomm* c, void* const* buf, uint64_t nbytes, int root,
@@ -563,22 +712,17 @@ int fmpi_bcast_any(const fmpi_devcomm* c, void* const* buf, uint64_t nbytes, int
   for (uint64_t done = 0; done < nbytes && rc == 0; done += chunk) {
     const uint64_t n = nbytes - done < chunk ? nbytes - done : chunk;
     PtrTable t{};
-    for (int i = 0; i < n_ranks; ++i) t.p[i] = static_cast<uint8_t*>(buf[i]) + done;
-    if (reinterpret_cast<uintptr_t>(t.p[0]) % 16)
-      return set_error("bcast buffer must be 16-byte aligned");
-    const int sag = (algo == FMPI_ALGO_TWOSHOT || (algo == FMPI_ALGO_AUTO && n >= (1u << 20))) &&
-                    c->world > 2;
+    for (int i = 0; i < n_ranks; ++i) {
+      t.p[i] = static_cast<uint8_t*>(buf[i]) + done;
+      if (reinterpret_cast<uintptr_t>(t.p[i]) % 16) return set_error("bcast buffer must be 16-byte aligned");
+    }
+    const int mode = bcast_mode(c, algo, n);
+    if (mode < 0) return set_error("multicast broadcast requested but no multicast mapping");
     const Shape s = pick_shape(c, l, n);
     rc = launch_ranked(bcast_stage_kernel, *c, s.blocks, s.threads, static_cast<cudaStream_t>(st),
-                       *c, t, n, root, stage_off, half, sag);
+                       *c, t, n, root, stage_off, half, mode);
   }
   return rc;
-}
-
-__global__ void flush_l2_kernel(uint4* p, uint64_t nvec, uint32_t salt) {
-  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
-  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride)
-    p[i] = make_uint4(salt, uint32_t(i), salt ^ uint32_t(i), 0);
 }
 
 int fmpi_flush_l2(void* buf, uint64_t nbytes, fmpi_stream st) {

@@ -244,6 +244,37 @@ template <> struct VecOps<int16_t> : IntVecOps<int16_t, 8> {};
 template <> struct VecOps<int8_t> : IntVecOps<int8_t, 16> {};
 template <> struct VecOps<uint8_t> : IntVecOps<uint8_t, 16> {};
 
+// ---- in-switch reduction / multicast store (NVLS)
+template <typename T> struct Multimem;
+template <> struct Multimem<float> {
+  __device__ static uint4 ld_reduce(const void* mc) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+    return v;
+  }
+};
+template <> struct Multimem<__nv_bfloat16> {
+  __device__ static uint4 ld_reduce(const void* mc) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+    return v;
+  }
+};
+template <> struct Multimem<__half> {
+  __device__ static uint4 ld_reduce(const void* mc) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
+    return v;
+  }
+};
+__device__ __forceinline__ void multimem_st(void* mc, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
 __host__ __device__ inline size_t dtype_size(int dt) {
   switch (dt) {
     case FMPI_F32: case FMPI_I32: return 4;

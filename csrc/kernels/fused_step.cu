@@ -77,37 +77,6 @@ template <> struct RuleState<FMPI_RULE_DESCENT> { static constexpr bool kM = fal
 template <> struct RuleState<FMPI_RULE_ADAM> { static constexpr bool kM = true, kV = true; };
 template <> struct RuleState<FMPI_RULE_ADAMW> { static constexpr bool kM = true, kV = true; };
 
-// ---- in-switch reduction / multicast store (NVLS)
-template <typename T> struct Multimem;
-template <> struct Multimem<float> {
-  __device__ static uint4 ld_reduce(const void* mc) {
-    uint4 v;
-    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
-    return v;
-  }
-};
-template <> struct Multimem<__nv_bfloat16> {
-  __device__ static uint4 ld_reduce(const void* mc) {
-    uint4 v;
-    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
-    return v;
-  }
-};
-template <> struct Multimem<__half> {
-  __device__ static uint4 ld_reduce(const void* mc) {
-    uint4 v;
-    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc) : "memory");
-    return v;
-  }
-};
-__device__ __forceinline__ void multimem_st(void* mc, uint4 v) {
-  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x),
-               "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
-
 template <typename T, bool kMaster, int kRule, bool kNvls>
 __global__ void __launch_bounds__(512)
 fused_step_kernel(fmpi_devcomm c, FusedArgs a) {

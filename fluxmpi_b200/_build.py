@@ -43,11 +43,29 @@ def _nvcc() -> str | None:
 
 
 def _digest(paths) -> str:
+    # repo-relative names: the tree is copied to a different absolute path on the GPU box and
+    # the libraries built here must count as fresh there
     h = hashlib.sha256()
-    for p in sorted(str(x) for x in paths):
+    for p in sorted(str(Path(x).resolve().relative_to(ROOT)) for x in paths):
         h.update(p.encode())
-        h.update(Path(p).read_bytes())
+        h.update((ROOT / p).read_bytes())
     return h.hexdigest()
+
+
+class _BuildLock:
+    """One builder at a time (N ranks import the package concurrently)."""
+
+    def __enter__(self):
+        import fcntl
+        LIB.mkdir(exist_ok=True)
+        self.f = open(LIB / ".build.lock", "w")
+        fcntl.flock(self.f, fcntl.LOCK_EX)
+        return self
+
+    def __exit__(self, *a):
+        import fcntl
+        fcntl.flock(self.f, fcntl.LOCK_UN)
+        self.f.close()
 
 
 def _stale(out: Path, srcs, extra=()) -> bool:
@@ -71,12 +89,17 @@ def build_host(force: bool = False, verbose: bool = False) -> Path:
     srcs = [CSRC / s for s in HOST_SOURCES]
     if not force and not _stale(out, srcs, _headers()):
         return out
-    cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-pthread",
-           f"-I{INC}", *map(str, srcs), "-o", str(out), "-lrt"]
-    if verbose:
-        print(" ".join(cmd), file=sys.stderr)
-    subprocess.run(cmd, check=True)
-    _mark(out, srcs, _headers())
+    with _BuildLock():
+        if not force and not _stale(out, srcs, _headers()):
+            return out
+        tmp = out.with_suffix(f".so.tmp{os.getpid()}")
+        cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-pthread",
+               f"-I{INC}", *map(str, srcs), "-o", str(tmp), "-lrt"]
+        if verbose:
+            print(" ".join(cmd), file=sys.stderr)
+        subprocess.run(cmd, check=True)
+        os.replace(tmp, out)
+        _mark(out, srcs, _headers())
     return out
 
 
@@ -90,6 +113,13 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path | None:
     nvcc = _nvcc()
     if nvcc is None:
         return out if out.exists() else None
+    with _BuildLock():
+        if not force and not _stale(out, srcs, _headers()):
+            return out
+        return _build_cuda_locked(nvcc, out, srcs, verbose)
+
+
+def _build_cuda_locked(nvcc: str, out: Path, srcs, verbose: bool) -> Path:
     objs = []
     objdir = LIB / "obj"
     objdir.mkdir(exist_ok=True)
@@ -108,11 +138,13 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path | None:
     for p, cmd in procs:
         if p.wait() != 0:
             raise subprocess.CalledProcessError(p.returncode, cmd)
-    link = [nvcc, "-shared", *NVCC_ARCH, "-o", str(out), *map(str, objs), "-cudart", "static",
+    tmp = out.with_suffix(f".so.tmp{os.getpid()}")
+    link = [nvcc, "-shared", *NVCC_ARCH, "-o", str(tmp), *map(str, objs), "-cudart", "static",
             "-lpthread", "-ldl", "-lrt"]
     if verbose:
         print(" ".join(link), file=sys.stderr)
     subprocess.run(link, check=True)
+    os.replace(tmp, out)
     _mark(out, srcs, _headers())
     return out
 

@@ -32,6 +32,7 @@ import torch
 
 from .. import _native
 from .._native import DevComm, Launch, cuda_check
+from ..comm import _TORCH_DTYPES as _DT
 
 MB = 1 << 20
 
@@ -296,6 +297,13 @@ class DeviceWorld(_Base):
         self.comms = [self.comm_for(self.base, ch, data_offset=self.sig_bytes,
                                     data_bytes=self.base.size - self.sig_bytes)
                       for ch in range(_native.NUM_CHANNELS)]
+        # call-path caches: the eager collectives are latency-sensitive on the host side too
+        self._lib = lib
+        self._comm_refs = [C.byref(c) for c in self.comms]
+        self._lp_auto_obj = Launch(0, 0, _native.ALGO_AUTO)
+        self._lp_auto = C.byref(self._lp_auto_obj)
+        self._in1, self._out1 = C.c_void_p(), C.c_void_p()
+        self._in1_ref, self._out1_ref = C.byref(self._in1), C.byref(self._out1)
 
     def comm_for(self, seg: Segment, channel: int, data_offset: int = 0,
                  data_bytes: Optional[int] = None) -> DevComm:
@@ -340,29 +348,33 @@ class DeviceWorld(_Base):
 
     def _reduce_native(self, src: torch.Tensor, dst: torch.Tensor, op: int, root: int, channel: int,
                        stream=None, launch=None):
-        lib = _native.cuda()
-        comm = self.comms[channel]
-        st = _stream_ptr(stream)
-        code = _dtype_code(src.dtype)
+        lib = self._lib
+        comm = self._comm_refs[channel]
+        st = (torch.cuda.current_stream() if stream is None else stream).cuda_stream
+        code = _DT.get(src.dtype)
+        if code is None:
+            code = _dtype_code(src.dtype)
         es = src.element_size()
         n = src.numel()
         nbytes = n * es
         bulk = n if nbytes % 16 == 0 or nbytes <= (200 << 10) else (nbytes // 16 * 16) // es
-        lp = launch if launch is not None else self._launch()
-        parts = [(0, bulk)] + ([(bulk, n - bulk)] if bulk < n else [])
-        for off, cnt in parts:
-            if cnt == 0:
-                continue
-            i = C.c_void_p(src.data_ptr() + off * es)
-            o = C.c_void_p(dst.data_ptr() + off * es)
-            if root < 0:
-                rc = lib.fmpi_allreduce_any(C.byref(comm), C.byref(i), C.byref(o), cnt, code, op,
-                                            self.ar_off, self.ar_bytes, lp, st)
-            else:
-                rc = lib.fmpi_reduce_any(C.byref(comm), C.byref(i), C.byref(o), cnt, code, op, root,
-                                         self.ar_off, self.ar_bytes, lp, st)
-            cuda_check(rc, "allreduce" if root < 0 else "reduce")
-            _native.count_launch()
+        lp = launch if launch is not None else self._lp_auto
+        i, o = self._in1, self._out1     # reusable one-entry pointer tables (read at launch)
+        sp, dp = src.data_ptr(), dst.data_ptr()
+        off = 0
+        for cnt in ((bulk, n - bulk) if bulk < n else (bulk,)):
+            if cnt:
+                i.value, o.value = sp + off * es, dp + off * es
+                if root < 0:
+                    rc = lib.fmpi_allreduce_any(comm, self._in1_ref, self._out1_ref, cnt, code, op,
+                                                self.ar_off, self.ar_bytes, lp, st)
+                else:
+                    rc = lib.fmpi_reduce_any(comm, self._in1_ref, self._out1_ref, cnt, code, op, root,
+                                             self.ar_off, self.ar_bytes, lp, st)
+                if rc:
+                    cuda_check(rc, "allreduce" if root < 0 else "reduce")
+                _native.launch_count += 1
+            off += cnt
 
     # ------------------------------------------------------------------ collectives (stream-ordered)
     def allreduce(self, t: torch.Tensor, op: int, launch=None):

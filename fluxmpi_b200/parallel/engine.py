@@ -147,7 +147,8 @@ class DataParallelEngine:
         else:
             self.state_tree = None   # built lazily by the unfused path
 
-        use_nvls = (algo == "nvls") or (algo == "auto" and bool(self.seg.mc_ptr) and self.world > 1)
+        # in-switch reduction moves ~N bytes per link instead of 2N(W-1)/W: a win from W = 4 up
+        use_nvls = (algo == "nvls") or (algo == "auto" and bool(self.seg.mc_ptr) and self.world >= 4)
         if algo == "nvls" and not self.seg.mc_ptr:
             raise RuntimeError("algo='nvls' requested but this world has no multicast mapping")
         self.algo = _native.ALGO_NVLS if use_nvls else _native.ALGO_TWOSHOT
