@@ -7,6 +7,8 @@
 // the result is deterministic run to run. The scratch buffer (fmpi_reduce_scratch_bytes(),
 // caller-allocated, zero-initialised once) holds the ticket word and the partials; the ticket
 // is reset by the last block so the buffer can be reused by the next call on the same stream.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace fmpi {
@@ -151,3 +153,86 @@ int fmpi_checksum(const void* x, uint64_t nbytes, uint64_t* out, void* scratch, 
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// fmpi_sumsq_noalloc — the same sum of squares for callers that must not allocate.
+//
+// Who that is: code running where a device allocation is either forbidden or would be a bug —
+// a Julia/CUDA.jl host that owns the memory pool and does not want a foreign library calling
+// the allocator behind its back, a logging hook that fires in the middle of a training step
+// whose memory has been planned to the byte, a monitoring thread that may run while another
+// thread is in an allocator-sensitive region. fmpi_sumsq asks such a caller to bring a scratch
+// buffer; this variant brings its own: a small array that lives in the library's device image.
+//
+// What to know before using it:
+//   * The scratch is ONE array per GPU (every GPU that loads this library holds these 2304
+//     bytes until the process exits) and every call on that GPU uses it. Two calls whose
+//     kernels can overlap on the device — different streams without an ordering between
+//     them — race on it and produce garbage. Calls on one stream are fine.
+//   * The array keeps whatever the previous call left behind. The only part that has to start
+//     from zero is the arrival ticket; each call clears it on its stream before the kernel.
+//   * At most FMPI_NOALLOC_MAX_COUNT elements per call; larger inputs are refused.
+//   * The first call on a device looks up the array's device address (once, with that device
+//     current). Make that first call outside of any stream capture.
+//   * Nothing here calls cudaMalloc, cudaFree or any allocating library routine. The caller
+//     still supplies the input and the 8-byte output.
+namespace fmpi {
+constexpr int kNoallocPartials = 256;
+constexpr size_t kNoallocBytes = 2304;  // 16 (ticket) + 8 * 256 partials, rounded up to 256
+static_assert(16 + sizeof(double) * kNoallocPartials <= kNoallocBytes, "scratch too small");
+}  // namespace fmpi
+
+// In host code this name is only a stand-in for the symbol, not a device address; the address
+// is obtained with cudaGetSymbolAddress below.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[fmpi::kNoallocBytes];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_noalloc_ptr[kMaxDevices];
+bool g_noalloc_ready[kMaxDevices];
+std::mutex g_noalloc_mu;
+
+// Once per device, with that device current.
+int noalloc_scratch(void** out) {
+  int dev = -1;
+  if (check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return 1;
+  if (dev < 0 || dev >= kMaxDevices) return set_error("device %d out of range", dev);
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ready[dev]) {
+    void* p = nullptr;
+    if (check_cuda(cudaGetSymbolAddress(&p, g_noalloc_scratch), "cudaGetSymbolAddress(noalloc scratch)"))
+      return 1;
+    g_noalloc_ptr[dev] = p;
+    g_noalloc_ready[dev] = true;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" int fmpi_sumsq_noalloc(const void* x, uint64_t count, int dtype, double* out,
+                                  fmpi_stream st) {
+  if (!out) return set_error("null output");
+  if (count > FMPI_NOALLOC_MAX_COUNT)
+    return set_error("fmpi_sumsq_noalloc: %llu elements exceed the limit of %llu; split the input "
+                     "or use fmpi_sumsq with a caller-provided scratch buffer",
+                     (unsigned long long)count, (unsigned long long)FMPI_NOALLOC_MAX_COUNT);
+  if (dtype != FMPI_F32 && dtype != FMPI_F64 && dtype != FMPI_BF16 && dtype != FMPI_F16)
+    return set_error("sumsq: unsupported dtype %d", dtype);
+  void* scratch = nullptr;
+  if (noalloc_scratch(&scratch)) return 1;
+  cudaStream_t s = static_cast<cudaStream_t>(st);
+  // the ticket must be zero when the kernel starts, whatever an earlier call left there
+  if (check_cuda(cudaMemsetAsync(scratch, 0, 16, s), "cudaMemsetAsync(noalloc ticket)")) return 1;
+  unsigned int* ticket = static_cast<unsigned int*>(scratch);
+  double* partials = reinterpret_cast<double*>(static_cast<uint8_t*>(scratch) + 16);
+  uint64_t want = (count + 512 * 8 - 1) / (512 * 8);
+  const int blocks = int(want < 1 ? 1 : want > fmpi::kNoallocPartials ? fmpi::kNoallocPartials : want);
+  switch (dtype) {
+    case FMPI_F32: sumsq_kernel<float><<<blocks, 512, 0, s>>>(static_cast<const float*>(x), count, out, ticket, partials); break;
+    case FMPI_F64: sumsq_kernel<double><<<blocks, 512, 0, s>>>(static_cast<const double*>(x), count, out, ticket, partials); break;
+    case FMPI_BF16: sumsq_kernel<__nv_bfloat16><<<blocks, 512, 0, s>>>(static_cast<const __nv_bfloat16*>(x), count, out, ticket, partials); break;
+    default: sumsq_kernel<__half><<<blocks, 512, 0, s>>>(static_cast<const __half*>(x), count, out, ticket, partials); break;
+  }
+  return check_cuda(cudaGetLastError(), "sumsq_noalloc launch");
+}

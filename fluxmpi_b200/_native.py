@@ -193,6 +193,7 @@ def cuda():
         lib.fmpi_reduce_scratch_bytes.restype = C.c_size_t
         lib.fmpi_sumsq.argtypes = [vp, u64, i32, vp, vp, vp]
         lib.fmpi_checksum.argtypes = [vp, u64, vp, vp, vp]
+        lib.fmpi_sumsq_noalloc.argtypes = [vp, u64, i32, vp, vp]
         lib.fmpi_flush_l2.argtypes = [vp, u64, vp]
         _cuda = lib
     return _cuda

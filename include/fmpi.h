@@ -219,6 +219,20 @@ int fmpi_sumsq(const void* x, uint64_t count, int dtype, double* out, void* scra
                fmpi_stream st);
 int fmpi_checksum(const void* x, uint64_t nbytes, uint64_t* out, void* scratch, fmpi_stream st);
 
+/* fmpi_sumsq for callers that must not allocate device memory (no counterpart in the
+ * reference, which has no device code of its own): a host runtime that owns the GPU memory
+ * pool, a hook running inside a step whose memory is fully planned, a monitoring thread.
+ * Same result as fmpi_sumsq, but the scratch is a 2304-byte array inside the library's device
+ * image instead of a caller buffer, so the call performs no cudaMalloc / cudaFree / allocating
+ * library call; the caller passes only the input and the 8-byte device output.
+ *   - at most FMPI_NOALLOC_MAX_COUNT elements, more is refused with an error;
+ *   - one scratch array per GPU, shared by all calls: calls that can overlap on the device
+ *     (unordered streams) race; calls on one stream are safe;
+ *   - the first call on a device resolves the array's address (once per device, with that
+ *     device current): issue it before starting any stream capture. */
+#define FMPI_NOALLOC_MAX_COUNT (1ull << 28)
+int fmpi_sumsq_noalloc(const void* x, uint64_t count, int dtype, double* out, fmpi_stream st);
+
 /* Write > L2-size bytes (bench hygiene: flush L2 between timed iterations). */
 int fmpi_flush_l2(void* buf, uint64_t nbytes, fmpi_stream st);
 
