@@ -76,6 +76,7 @@ def main():
     ap.add_argument("--ops", default="allreduce,bcast,reduce")
     ap.add_argument("--no-nccl", action="store_true")
     ap.add_argument("--graph", action="store_true", help="time CUDA-graph replays (no host launch cost)")
+    ap.add_argument("--symm", action="store_true", help="our buffers come from fm.symm_empty (registered memory)")
     a = ap.parse_args()
 
     fm.Init()
@@ -96,11 +97,20 @@ def main():
         sizes.append(s)
         s *= 4
     rows = []
+    symm_pool: dict = {}
     pool_bytes = 192 << 20
     for nbytes in sizes:
         n = nbytes // es
         nbuf = max(1, min(64, pool_bytes // nbytes))
-        bufs = [torch.ones(n, dtype=dt, device=dev) for _ in range(nbuf)]
+        if a.symm:      # buffers in symmetric memory: in-place NVLink kernels, no staging copies
+            nbuf = max(1, min(nbuf, 4))
+            if nbytes not in symm_pool:
+                symm_pool[nbytes] = [fm.symm_empty(n, dt) for _ in range(nbuf)]
+            bufs = symm_pool[nbytes]
+            for b in bufs:
+                b.fill_(1)
+        else:
+            bufs = [torch.ones(n, dtype=dt, device=dev) for _ in range(nbuf)]
         iters = 200 if nbytes <= (1 << 20) else 40 if nbytes <= (64 << 20) else 10
         warm = max(3, iters // 10)
         row = {"bytes": nbytes, "world": w}

@@ -512,11 +512,14 @@ bool nvls_capable(const fmpi_devcomm* c, int dtype, int op) {
          (dtype == FMPI_F32 || dtype == FMPI_BF16 || dtype == FMPI_F16);
 }
 
-// AUTO picks the in-switch path where it moves fewer bytes per link (W >= 4) and the message
-// is past the latency regime; the Python tuner can override either way.
-bool want_nvls(const fmpi_devcomm* c, int algo, int dtype, int op, uint64_t nbytes) {
+// AUTO defaults from the measured grid (profiles/tune_*.json): on a symmetric region the
+// in-switch path wins from W = 4 up (665 vs 624 GB/s bus bandwidth at 256 MB, with 16 CTAs);
+// through staging the P2P two-shot wins at W <= 4 because the NVLS variant pays a copy-in.
+// The Python tuner (parallel/tuner.py) overrides this with the table measured on the box.
+bool want_nvls(const fmpi_devcomm* c, int algo, int dtype, int op, uint64_t nbytes, bool symm) {
   if (algo == FMPI_ALGO_NVLS) return true;
-  return algo == FMPI_ALGO_AUTO && nvls_capable(c, dtype, op) && c->world >= 4 && nbytes >= (512u << 10);
+  if (algo != FMPI_ALGO_AUTO || !nvls_capable(c, dtype, op)) return false;
+  return symm ? (c->world >= 4 && nbytes >= (256u << 10)) : (c->world >= 8 && nbytes >= (4u << 20));
 }
 
 #define FMPI_DISPATCH_DTYPE(dt, EXPR)                                   \
@@ -551,10 +554,11 @@ int reduce_symm_impl(const fmpi_devcomm* c, uint64_t off, uint64_t count, int dt
   const uint64_t nbytes = count * es, nvec = (nbytes + 15) / 16;
   if (off + nvec * 16 > c->data_bytes) return set_error("region exceeds the symmetric window");
   if (count == 0) return 0;
-  const Shape s = pick_shape(c, l, nbytes / c->world);
+  Shape s = pick_shape(c, l, nbytes / c->world);
   int rc = 0;
-  if (want_nvls(c, l ? l->algo : FMPI_ALGO_AUTO, dtype, op, nbytes)) {
+  if (want_nvls(c, l ? l->algo : FMPI_ALGO_AUTO, dtype, op, nbytes, true)) {
     if (!nvls_capable(c, dtype, op)) return set_error("NVLS requested but not possible for this call");
+    if (!(l && l->blocks > 0) && s.blocks > 16) s.blocks = 16;  // the switch does the work: few CTAs suffice
     FMPI_DISPATCH_NVLS(dtype, rc = launch_ranked(nvls_symm_kernel<T>, *c, s.blocks, s.threads, st, *c,
                                                  off, nvec, dest_root));
     return rc;
@@ -604,7 +608,7 @@ int reduce_any_impl(const fmpi_devcomm* c, const void* const* in, void* const* o
     return set_error("two-shot path needs a multiple of 16 bytes (got %llu); split off the tail",
                      (unsigned long long)nbytes);
   const uint64_t ts_off = stage_off + os_bytes, ts_bytes = stage_bytes - os_bytes;
-  const bool nvls = want_nvls(c, algo, dtype, op, nbytes);
+  const bool nvls = want_nvls(c, algo, dtype, op, nbytes, false);
   if (nvls && !nvls_capable(c, dtype, op)) return set_error("NVLS requested but not possible for this call");
   // Chunked so that a chunk fits: P2P uses scatter (N, first half) + result (N, second half).
   // NVLS needs only N and lives in the SECOND half: a P2P call's unsynchronised scatter pushes

@@ -268,7 +268,9 @@ int fmpi_fused_step(const fmpi_devcomm* c, uint64_t g_off, int gdt, uint64_t p_o
   } else {
     const uint64_t per_block = uint64_t(threads) * 16 * 2;
     const uint64_t want = (slice_bytes + per_block - 1) / per_block;
-    const uint64_t cap = c->world == 1 ? 148 * 4 : 148;
+    // multi-GPU buckets run beside backward's kernels: a link-bound kernel needs only enough
+    // CTAs to keep NVLink busy (measured: 16-32 for the in-switch path, 32-64 for P2P)
+    const uint64_t cap = c->world == 1 ? 148 * 4 : (nvls ? 32 : 64);
     blocks = int(want < 1 ? 1 : want > cap ? cap : want);
   }
   if (c->world > 1 && blocks > FMPI_MAX_BLOCKS) blocks = FMPI_MAX_BLOCKS;

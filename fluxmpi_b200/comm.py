@@ -274,6 +274,34 @@ def Ibcast(buf, root: int = 0, comm=COMM_WORLD):
     return buf, Request(future=fut, buffer=buf)
 
 
+# ------------------------------------------------------------------------------ symmetric tensors
+
+
+def symm_empty(shape, dtype=torch.float32):
+    """Collective allocation of a tensor in symmetric memory (every rank must call it with the
+    same shape, in the same order). Collectives on such tensors run in place over NVLink with
+    no staging copies (the analogue of MPI/NCCL registered buffers; the reference has none).
+    On a CPU-only world or in NCCL-fallback mode this is a plain ``torch.empty``."""
+    if not runtime.Initialized():
+        raise runtime.FluxMPINotInitializedError()
+    dw = runtime.state().device_world
+    if dw is None or not dw.native:
+        return torch.empty(shape, dtype=dtype, device=runtime.current_device())
+    return dw.symm_empty(shape, dtype)
+
+
+def symm_zeros(shape, dtype=torch.float32):
+    t = symm_empty(shape, dtype)
+    t.zero_()
+    return t
+
+
+def is_symmetric(t) -> bool:
+    dw = runtime.state().device_world
+    return bool(dw is not None and dw.native and isinstance(t, torch.Tensor) and t.is_cuda
+                and dw.find_symmetric(t) is not None)
+
+
 # Julia-style aliases so reference scripts translate 1:1 (`allreduce!` → `allreduce_b`).
 allreduce = allreduce_
 bcast = bcast_

@@ -117,6 +117,9 @@ class DeviceWorld(_Base):
         self._tables: dict = {}
         self._closed = False
         self.why_fallback = ""
+        self._heap = None                 # [segment, bump offset] for symm_empty
+        self._symm_regs: list = []        # registered symmetric segments (user-visible tensors)
+        self.tuner = None
 
     # ------------------------------------------------------------------ bring-up
     def _topology(self):
@@ -297,6 +300,8 @@ class DeviceWorld(_Base):
         self.comms = [self.comm_for(self.base, ch, data_offset=self.sig_bytes,
                                     data_bytes=self.base.size - self.sig_bytes)
                       for ch in range(_native.NUM_CHANNELS)]
+        from .tuner import Tuner
+        self.tuner = Tuner(self.world, self.has_multicast)
         # call-path caches: the eager collectives are latency-sensitive on the host side too
         self._lib = lib
         self._comm_refs = [C.byref(c) for c in self.comms]
@@ -358,7 +363,11 @@ class DeviceWorld(_Base):
         n = src.numel()
         nbytes = n * es
         bulk = n if nbytes % 16 == 0 or nbytes <= (200 << 10) else (nbytes // 16 * 16) // es
-        lp = launch if launch is not None else self._lp_auto
+        if launch is not None:
+            lp = launch
+        else:
+            tl = self.tuner.launch("allreduce_any" if root < 0 else "reduce_any", nbytes)
+            lp = tl[0] if tl else self._lp_auto
         i, o = self._in1, self._out1     # reusable one-entry pointer tables (read at launch)
         sp, dp = src.data_ptr(), dst.data_ptr()
         off = 0
@@ -377,9 +386,72 @@ class DeviceWorld(_Base):
             off += cnt
 
     # ------------------------------------------------------------------ collectives (stream-ordered)
+    # ------------------------------------------------------------------ symmetric tensors
+    def symm_empty(self, shape, dtype=torch.float32) -> torch.Tensor:
+        """Collective: a tensor in symmetric memory (same offset on every rank). Collectives on
+        such tensors run in place over NVLink with no staging copies — the analogue of NCCL's
+        registered user buffers. Every rank must make the same sequence of symm_empty calls."""
+        numel = 1
+        for s in (shape if isinstance(shape, (tuple, list, torch.Size)) else (shape,)):
+            numel *= int(s)
+        nbytes = _align(max(numel, 1) * torch.empty((), dtype=dtype).element_size(), 256)
+        heap = self._heap
+        if heap is None or heap[1] + nbytes > heap[0].size:
+            size = max(nbytes, int(os.environ.get("FMPI_SYMM_HEAP_MB", 256)) * MB)
+            seg = self.alloc_segment(size)
+            self._register(seg)
+            heap = self._heap = [seg, 0]
+        seg, off = heap
+        heap[1] = off + nbytes
+        raw = self.symm_tensor(seg, off, numel * torch.empty((), dtype=dtype).element_size())
+        return raw.view(dtype).view(shape)
+
+    def _register(self, seg: Segment):
+        comms = [self.comm_for(seg, ch) for ch in range(_native.NUM_CHANNELS)]
+        self._symm_regs.append((seg.local_ptr, seg.local_ptr + seg.size, seg, comms,
+                                [C.byref(c) for c in comms]))
+
+    def find_symmetric(self, t: torch.Tensor):
+        """(segment comm refs, byte offset) if ``t`` lives in a registered symmetric segment."""
+        p = t.data_ptr()
+        for lo, hi, seg, comms, refs in self._symm_regs:
+            if lo <= p < hi:
+                return refs, p - lo
+        return None
+
+    def _symm_collective(self, kind: str, t: torch.Tensor, hit, op: int, root: int, channel: int, stream):
+        refs, off = hit
+        lib = self._lib
+        nbytes = t.numel() * t.element_size()
+        st = (torch.cuda.current_stream() if stream is None else stream).cuda_stream
+        tl = self.tuner.launch("bcast_symm" if kind == "bcast" else "allreduce_symm", nbytes)
+        lp = tl[0] if tl else self._lp_auto
+        if kind == "bcast":
+            rc = lib.fmpi_bcast_symm(refs[channel], off, nbytes, root, lp, st)
+        elif root < 0:
+            rc = lib.fmpi_allreduce_symm(refs[channel], off, t.numel(), _DT[t.dtype], op, lp, st)
+        else:
+            rc = lib.fmpi_reduce_symm(refs[channel], off, t.numel(), _DT[t.dtype], op, root, lp, st)
+        if rc:
+            cuda_check(rc, kind)
+        _native.launch_count += 1
+
+    def _symm_hit(self, t: torch.Tensor):
+        if not self._symm_regs or not t.is_contiguous() or t.dtype == torch.bool:
+            return None
+        hit = self.find_symmetric(t)
+        if hit is None or hit[1] % 16 or (t.numel() * t.element_size()) % 16:
+            return None
+        return hit
+
     def allreduce(self, t: torch.Tensor, op: int, launch=None):
         if self.world == 1 or t.numel() == 0:
             return t
+        if self.native and launch is None:
+            hit = self._symm_hit(t)
+            if hit is not None:
+                self._symm_collective("allreduce", t.detach() if t.requires_grad else t, hit, op, -1, 0, None)
+                return t
         w, copy = self._work_tensor(t)
         if self.native:
             self._reduce_native(w, w, op, -1, 0, launch=launch)
@@ -392,6 +464,11 @@ class DeviceWorld(_Base):
     def reduce(self, t: torch.Tensor, op: int, root: int):
         if self.world == 1 or t.numel() == 0:
             return t
+        if self.native:
+            hit = self._symm_hit(t)
+            if hit is not None:
+                self._symm_collective("reduce", t.detach() if t.requires_grad else t, hit, op, root, 0, None)
+                return t
         w, copy = self._work_tensor(t)
         if self.native:
             self._reduce_native(w, w, op, root, 0)
@@ -407,14 +484,23 @@ class DeviceWorld(_Base):
     def bcast(self, t: torch.Tensor, root: int, channel: int = 0, stream=None):
         if self.world == 1 or t.numel() == 0:
             return t
+        if self.native:
+            hit = self._symm_hit(t)
+            if hit is not None:
+                self._symm_collective("bcast", t.detach() if t.requires_grad else t, hit, 0, root, channel, stream)
+                return t
         w, copy = self._work_tensor(t)
         if self.native:
-            lib = _native.cuda()
-            p = C.c_void_p(w.data_ptr())
-            cuda_check(lib.fmpi_bcast_any(C.byref(self.comms[channel]), C.byref(p),
-                                          w.numel() * w.element_size(), root, self.bc_off,
-                                          self.bc_bytes, self._launch(), _stream_ptr(stream)), "bcast")
-            _native.count_launch()
+            lib = self._lib
+            nbytes = w.numel() * w.element_size()
+            tl = self.tuner.launch("bcast_any", nbytes)
+            self._in1.value = w.data_ptr()
+            rc = lib.fmpi_bcast_any(self._comm_refs[channel], self._in1_ref, nbytes, root, self.bc_off,
+                                    self.bc_bytes, tl[0] if tl else self._lp_auto,
+                                    (torch.cuda.current_stream() if stream is None else stream).cuda_stream)
+            if rc:
+                cuda_check(rc, "bcast")
+            _native.launch_count += 1
         else:
             self._nccl().broadcast(w, src=root)
         if copy and self.rank != root:

@@ -151,6 +151,14 @@ class DataParallelEngine:
         use_nvls = (algo == "nvls") or (algo == "auto" and bool(self.seg.mc_ptr) and self.world >= 4)
         if algo == "nvls" and not self.seg.mc_ptr:
             raise RuntimeError("algo='nvls' requested but this world has no multicast mapping")
+        # measured choice for in-place all-reduce of a bucket-sized symmetric region, if any
+        tuned = self.dw.tuner.choice("allreduce_symm", int(min(bucket_mb * (1 << 20), cur * es))) \
+            if (self.world > 1 and self.dw.tuner is not None) else None
+        if tuned is not None:
+            if algo == "auto":
+                use_nvls = tuned[0] == "nvls" and bool(self.seg.mc_ptr)
+            if blocks == 0 and ((tuned[0] == "nvls") == use_nvls):
+                self.blocks = tuned[1]
         self.algo = _native.ALGO_NVLS if use_nvls else _native.ALGO_TWOSHOT
 
         # ---- buckets in backward (reverse registration) order

@@ -112,6 +112,25 @@ fp = fm.FlatParams.from_tree({"a": torch.full((1000,), float(r), device=dev), "b
 fm.allreduce_gradients(fp)
 assert torch.equal(fp.b, torch.full((3, 3), float(w), device=dev))
 
+# tensors in symmetric memory: same calls, in-place kernels without staging
+if dw.native:
+    for n in (4, 1000, 1 << 20):
+        s = fm.symm_empty((n,), torch.float32)
+        assert fm.is_symmetric(s) and not fm.is_symmetric(torch.ones(4, device=dev))
+        s.fill_(float(r + 1))
+        fm.allreduce_(s, "sum")
+        assert torch.equal(s, torch.full((n,), w * (w + 1) / 2, device=dev)), n
+        s.fill_(float(r))
+        fm.bcast_(s, w - 1)
+        assert torch.equal(s, torch.full((n,), float(w - 1), device=dev))
+        s.fill_(float(r + 1))
+        fm.reduce_(s, "max", 0)
+        assert torch.equal(s, torch.full((n,), float(w if r == 0 else r + 1), device=dev))
+    hb = fm.symm_empty((3, 1024), torch.bfloat16)
+    hb.fill_(1.0)
+    fm.allreduce_(hb, "+")
+    assert hb.shape == (3, 1024) and torch.equal(hb, torch.full((3, 1024), float(w), dtype=torch.bfloat16, device=dev))
+
 torch.cuda.synchronize()
 fm.Finalize()
 print("RANK_OK", r)
