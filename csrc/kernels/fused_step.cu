@@ -184,6 +184,80 @@ fused_step_kernel(fmpi_devcomm c, FusedArgs a) {
   }
 }
 
+// World of one: no peers, no barriers — a pure HBM stream (read g, p, m, v; write p, m, v and
+// the cleared g: 32 B/element for fp32 Adam). Written separately so it does not carry the
+// 8-rank load arrays of the multi-GPU kernel (88 registers -> 1 CTA/SM, measured 3.4 TB/s):
+// U vectors are loaded back to back before any arithmetic to keep enough bytes in flight.
+template <typename T, bool kMaster, int kRule>
+__global__ void __launch_bounds__(256)
+fused_step_local_kernel(fmpi_devcomm c, FusedArgs a) {
+  using V = VecOps<T>;
+  constexpr int N = V::kN;
+  constexpr int U = N == 4 ? 4 : 2;
+  RuleMath<kRule> rule;
+  rule.init(a.h, a.step[0] ? *a.step[0] : 0);
+  const uint64_t nvec = (a.hi - a.lo) / N;
+  uint8_t* gp = byte_ptr(c.data[0], a.g_off + a.lo * sizeof(T));
+  uint8_t* pp = byte_ptr(c.data[0], a.p_off + a.lo * sizeof(T));
+  float* __restrict__ mloc = a.m[0];
+  float* __restrict__ vloc = a.v[0];
+  float* __restrict__ mst = a.master[0];
+  const bool zero = a.h.zero_grad != 0;
+  const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+  for (uint64_t i0 = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i0 < nvec; i0 += U * stride) {
+    uint4 graw[U], praw[U];
+    float p[U][N], m[U][N], v[U][N];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint64_t i = i0 + u * stride;
+      if (i < nvec) {
+        const uint64_t e = a.lo + i * N;
+        graw[u] = ld_stream(gp + i * 16);
+        if (kMaster) {
+#pragma unroll
+          for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(&p[u][k]) = *reinterpret_cast<const float4*>(mst + e + k);
+        } else {
+          praw[u] = ld_stream(pp + i * 16);
+        }
+        if (RuleState<kRule>::kM) {
+#pragma unroll
+          for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(&m[u][k]) = *reinterpret_cast<const float4*>(mloc + e + k);
+        }
+        if (RuleState<kRule>::kV) {
+#pragma unroll
+          for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(&v[u][k]) = *reinterpret_cast<const float4*>(vloc + e + k);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const uint64_t i = i0 + u * stride;
+      if (i < nvec) {
+        const uint64_t e = a.lo + i * N;
+        float g[N];
+        V::unpack(graw[u], g);
+        if (!kMaster) V::unpack(praw[u], p[u]);
+#pragma unroll
+        for (int k = 0; k < N; ++k) p[u][k] = rule.step(p[u][k], g[k], m[u][k], v[u][k]);
+        if (RuleState<kRule>::kM) {
+#pragma unroll
+          for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(mloc + e + k) = *reinterpret_cast<float4*>(&m[u][k]);
+        }
+        if (RuleState<kRule>::kV) {
+#pragma unroll
+          for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(vloc + e + k) = *reinterpret_cast<float4*>(&v[u][k]);
+        }
+        if (kMaster) {
+#pragma unroll
+          for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(mst + e + k) = *reinterpret_cast<float4*>(&p[u][k]);
+        }
+        st_stream(pp + i * 16, V::pack(p[u]));
+        if (zero) st_stream(gp + i * 16, make_uint4(0, 0, 0, 0));
+      }
+    }
+  }
+}
+
 __global__ void step_advance_kernel(int64_t* s) { *s += 1; }
 
 }  // namespace fmpi
@@ -278,17 +352,22 @@ int fmpi_fused_step(const fmpi_devcomm* c, uint64_t g_off, int gdt, uint64_t p_o
   cudaStream_t st = static_cast<cudaStream_t>(stream);
 
   if (c->world == 1) {
-    // no peers: plain launch, any grid size (launch_ranked clamps to the signal-pad rows)
+    // no peers: the local streaming kernel, sized to fill the chip (256-thread CTAs, several
+    // resident per SM, a few waves)
     fmpi_devcomm c1 = *c;
     c1.emulate = 0;
     c1.rank = 0;
+    const int lthreads = 256;
+    const uint64_t nvec1 = (hi - lo) / N;
+    uint64_t want1 = (nvec1 + uint64_t(lthreads) * 4 - 1) / (uint64_t(lthreads) * 4);
+    const int lblocks = (l && l->blocks > 0) ? l->blocks : int(want1 < 1 ? 1 : want1 > 148 * 8 ? 148 * 8 : want1);
 #define FMPI_W1(T, MASTER)                                                                      \
   switch (h->rule) {                                                                            \
-    case FMPI_RULE_DESCENT: fused_step_kernel<T, MASTER, FMPI_RULE_DESCENT, false><<<blocks, threads, 0, st>>>(c1, a); break;   \
-    case FMPI_RULE_MOMENTUM: fused_step_kernel<T, MASTER, FMPI_RULE_MOMENTUM, false><<<blocks, threads, 0, st>>>(c1, a); break; \
-    case FMPI_RULE_NESTEROV: fused_step_kernel<T, MASTER, FMPI_RULE_NESTEROV, false><<<blocks, threads, 0, st>>>(c1, a); break; \
-    case FMPI_RULE_ADAM: fused_step_kernel<T, MASTER, FMPI_RULE_ADAM, false><<<blocks, threads, 0, st>>>(c1, a); break;         \
-    case FMPI_RULE_ADAMW: fused_step_kernel<T, MASTER, FMPI_RULE_ADAMW, false><<<blocks, threads, 0, st>>>(c1, a); break;       \
+    case FMPI_RULE_DESCENT: fused_step_local_kernel<T, MASTER, FMPI_RULE_DESCENT><<<lblocks, lthreads, 0, st>>>(c1, a); break;   \
+    case FMPI_RULE_MOMENTUM: fused_step_local_kernel<T, MASTER, FMPI_RULE_MOMENTUM><<<lblocks, lthreads, 0, st>>>(c1, a); break; \
+    case FMPI_RULE_NESTEROV: fused_step_local_kernel<T, MASTER, FMPI_RULE_NESTEROV><<<lblocks, lthreads, 0, st>>>(c1, a); break; \
+    case FMPI_RULE_ADAM: fused_step_local_kernel<T, MASTER, FMPI_RULE_ADAM><<<lblocks, lthreads, 0, st>>>(c1, a); break;         \
+    case FMPI_RULE_ADAMW: fused_step_local_kernel<T, MASTER, FMPI_RULE_ADAMW><<<lblocks, lthreads, 0, st>>>(c1, a); break;       \
     default: return set_error("rule %d has no fused kernel", h->rule);                          \
   }
     if (gdt == FMPI_F32) { FMPI_W1(float, false) }

@@ -63,11 +63,38 @@ template <typename T>
 __global__ void __launch_bounds__(512)
 sumsq_kernel(const T* __restrict__ x, uint64_t n, double* out, unsigned int* ticket, double* partials) {
   __shared__ double sh[32];
+  using V = VecOps<T>;
+  constexpr int N = V::kN;
   double acc = 0.0;
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
-  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const double v = to_double(x[i]);
-    acc += v * v;
+  const uint64_t gtid = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  // scalar head up to the first 16-byte boundary, 16-byte vectors (4 in flight per thread:
+  // this is a pure HBM read stream), scalar tail
+  const uint64_t mis = reinterpret_cast<uintptr_t>(x) % 16;
+  uint64_t head = mis ? (16 - mis) / sizeof(T) : 0;
+  if (head > n) head = n;
+  const uint64_t nvec = (n - head) / N;
+  const uint8_t* xv = reinterpret_cast<const uint8_t*>(x + head);
+  for (uint64_t i = gtid; i < nvec; i += 4 * stride) {
+    uint4 raw[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + u * stride < nvec) raw[u] = ld_stream(xv + (i + u * stride) * 16);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + u * stride < nvec) {
+        typename V::Acc e[N];
+        V::unpack(raw[u], e);
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          const double d = double(e[k]);
+          acc += d * d;
+        }
+      }
+  }
+  if (gtid == 0) {
+    for (uint64_t i = 0; i < head; ++i) { const double d = to_double(x[i]); acc += d * d; }
+    for (uint64_t i = head + nvec * N; i < n; ++i) { const double d = to_double(x[i]); acc += d * d; }
   }
   acc = block_sum(acc, sh);
   if (threadIdx.x == 0) partials[blockIdx.x] = acc;
@@ -92,10 +119,33 @@ checksum_kernel(const uint8_t* __restrict__ x, uint64_t nbytes, uint64_t* out, u
   const uint64_t nwords = nbytes / 4;
   const uint32_t* w = reinterpret_cast<const uint32_t*>(x);
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
-  for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nwords; i += stride)
-    acc += (uint64_t(w[i]) + 0x9E3779B97F4A7C15ull) * (2 * i + 1);
-  if (blockIdx.x == 0 && threadIdx.x == 0)
+  const uint64_t gtid = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+  // word i contributes (w[i] + C) * (2i + 1): position sensitive, order independent, so the
+  // bulk can be read as 16-byte vectors (4 in flight) around a scalar head / tail
+  const uint64_t mis = (reinterpret_cast<uintptr_t>(x) % 16) / 4;
+  uint64_t head = mis ? 4 - mis : 0;
+  if (head > nwords) head = nwords;
+  const uint64_t nvec = (nwords - head) / 4;
+  const uint8_t* xv = reinterpret_cast<const uint8_t*>(w + head);
+  for (uint64_t i = gtid; i < nvec; i += 4 * stride) {
+    uint4 raw[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + u * stride < nvec) raw[u] = ld_stream(xv + (i + u * stride) * 16);
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (i + u * stride < nvec) {
+        const uint64_t w0 = head + (i + u * stride) * 4;
+        const uint32_t ws[4] = {raw[u].x, raw[u].y, raw[u].z, raw[u].w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) acc += (uint64_t(ws[k]) + 0x9E3779B97F4A7C15ull) * (2 * (w0 + k) + 1);
+      }
+  }
+  if (gtid == 0) {
+    for (uint64_t i = 0; i < head; ++i) acc += (uint64_t(w[i]) + 0x9E3779B97F4A7C15ull) * (2 * i + 1);
+    for (uint64_t i = head + nvec * 4; i < nwords; ++i) acc += (uint64_t(w[i]) + 0x9E3779B97F4A7C15ull) * (2 * i + 1);
     for (uint64_t k = nwords * 4; k < nbytes; ++k) acc += (uint64_t(x[k]) + 0x51ull) * (2 * k + 1);
+  }
   acc = block_sum_u64(acc, sh);
   if (threadIdx.x == 0) partials[blockIdx.x] = acc;
   if (take_ticket(ticket)) {
