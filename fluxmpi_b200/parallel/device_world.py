@@ -451,7 +451,10 @@ class DeviceWorld(_Base):
     # the cost of staging hides behind the link time instead of adding to it (measured at 8
     # GPUs, 1 GiB: in-place symmetric all-reduce 837 GB/s bus bandwidth vs 510 GB/s for the
     # single-kernel staged path).
-    PIPE_MIN_BYTES = int(float(os.environ.get("FMPI_PIPELINE_MIN_MB", 48)) * MB)
+    # Off by default (0): measured at 4 GPUs the per-chunk kernel overheads eat the overlap
+    # (256 MB: 860 us pipelined vs 833 us single staged kernel vs 645 us in place on symmetric
+    # memory). Set FMPI_PIPELINE_MIN_MB to opt in; fm.symm_empty is the real fix.
+    PIPE_MIN_BYTES = int(float(os.environ.get("FMPI_PIPELINE_MIN_MB", 0)) * MB)
     PIPE_CHUNK_BYTES = int(float(os.environ.get("FMPI_PIPELINE_CHUNK_MB", 32)) * MB)
 
     def _pipe_setup(self):
@@ -505,8 +508,8 @@ class DeviceWorld(_Base):
         t.record_stream(s_out)
 
     def _pipe_ok(self, t: torch.Tensor) -> bool:
-        return (self.native and self.world > 1 and t.is_contiguous() and t.dtype != torch.bool
-                and t.numel() * t.element_size() >= self.PIPE_MIN_BYTES
+        return (self.PIPE_MIN_BYTES > 0 and self.native and self.world > 1 and t.is_contiguous()
+                and t.dtype != torch.bool and t.numel() * t.element_size() >= self.PIPE_MIN_BYTES
                 and self.PIPE_CHUNK_BYTES > 0)
 
     def _symm_hit(self, t: torch.Tensor):

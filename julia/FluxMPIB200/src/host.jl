@@ -1,0 +1,83 @@
+# Host world (POSIX shm): what MPI.Init / MPI.Allreduce! / MPI.Bcast! / MPI.Reduce! / MPI.Barrier
+# are to the reference (src/common.jl:22,91; src/mpi_extensions.jl:108-111,130-133,152-155).
+
+mutable struct World
+    rank::Int
+    size::Int
+    local_rank::Int
+    host::Ptr{Cvoid}          # fmpi_host_comm*
+    device::Any               # DeviceWorld or nothing
+    job::String
+end
+
+const WORLD = Ref{Union{Nothing, World}}(nothing)
+
+function _job_name()
+    haskey(ENV, "FMPI_JOB_ID") && return ENV["FMPI_JOB_ID"]
+    return string(get(ENV, "MASTER_PORT", "0"), "-", get(ENV, "TORCHELASTIC_RUN_ID", "none"), "-jl")
+end
+
+function _host_init()
+    rank = parse(Int, get(ENV, "RANK", "0"))
+    size = parse(Int, get(ENV, "WORLD_SIZE", "1"))
+    lrank = parse(Int, get(ENV, "LOCAL_RANK", string(rank)))
+    job = _job_name()
+    h = Ref{Ptr{Cvoid}}(C_NULL)
+    if size > 1
+        name = "/fmpi_" * replace(job, r"[^A-Za-z0-9]" => "_")
+        timeout = parse(Float64, get(ENV, "FMPI_TIMEOUT_S", "300"))
+        hcheck(ccall(hsym(:fmpi_host_init), Cint, (Cstring, Cint, Cint, Csize_t, Cdouble, Ptr{Ptr{Cvoid}}),
+                     name, rank, size, 8 << 20, timeout, h), "fmpi_host_init")
+    end
+    WORLD[] = World(rank, size, lrank, h[], nothing, job)
+    atexit(_finalize)
+    return WORLD[]
+end
+
+function _finalize()
+    w = WORLD[]
+    w === nothing && return
+    w.device === nothing || _device_close(w.device)
+    w.host == C_NULL || ccall(hsym(:fmpi_host_finalize), Cint, (Ptr{Cvoid},), w.host)
+    WORLD[] = nothing
+    return
+end
+
+function host_barrier()
+    w = WORLD[]
+    (w === nothing || w.size == 1) && return
+    hcheck(ccall(hsym(:fmpi_host_barrier), Cint, (Ptr{Cvoid},), w.host), "barrier")
+end
+
+function host_allgather(blob::Vector{UInt8})
+    w = WORLD[]
+    w.size == 1 && return [blob]
+    out = Vector{UInt8}(undef, length(blob) * w.size)
+    hcheck(ccall(hsym(:fmpi_host_allgather), Cint, (Ptr{Cvoid}, Ptr{UInt8}, Ptr{UInt8}, Csize_t),
+                 w.host, blob, out, length(blob)), "allgather")
+    return [out[(i * length(blob) + 1):((i + 1) * length(blob))] for i in 0:(w.size - 1)]
+end
+
+function _host_allreduce!(v::Array{T}, op) where {T}
+    w = WORLD[]
+    w.size == 1 && return v
+    hcheck(ccall(hsym(:fmpi_host_allreduce), Cint, (Ptr{Cvoid}, Ptr{T}, Ptr{T}, Csize_t, Cint, Cint),
+                 w.host, v, v, length(v), dtype_code(T), op_code(op)), "allreduce!")
+    return v
+end
+
+function _host_bcast!(v::Array{T}, root::Integer) where {T}
+    w = WORLD[]
+    w.size == 1 && return v
+    hcheck(ccall(hsym(:fmpi_host_bcast), Cint, (Ptr{Cvoid}, Ptr{T}, Csize_t, Cint),
+                 w.host, v, sizeof(v), root), "bcast!")
+    return v
+end
+
+function _host_reduce!(v::Array{T}, op, root::Integer) where {T}
+    w = WORLD[]
+    w.size == 1 && return v
+    hcheck(ccall(hsym(:fmpi_host_reduce), Cint, (Ptr{Cvoid}, Ptr{T}, Ptr{T}, Csize_t, Cint, Cint, Cint),
+                 w.host, v, v, length(v), dtype_code(T), op_code(op), root), "reduce!")
+    return v
+end

@@ -37,5 +37,11 @@ def test_ipc_mode_and_no_multicast():
     _run("gpu_collectives.py", 2, env={"FMPI_DISABLE_MULTICAST": "1"}, args=("quick",))
 
 
+def test_chunk_pipelined_large_message_path():
+    """Opt-in path: big arbitrary buffers through a two-slot symmetric arena on three streams."""
+    _run("gpu_collectives.py", 2, env={"FMPI_PIPELINE_MIN_MB": "0.2", "FMPI_PIPELINE_CHUNK_MB": "0.125"},
+         args=("quick",))
+
+
 def test_nccl_fallback_when_p2p_disabled():
     _run("gpu_collectives.py", 2, env={"FMPI_DISABLE_P2P": "1"}, args=("quick",))
