@@ -2,9 +2,11 @@ module FluxMPIB200FluxExt
 
 using Flux, FluxMPIB200, Functors
 
-# reference: ext/FluxMPIFluxExt.jl:6-8 — returns the unwrapped model
-function FluxMPIB200.synchronize!(x::FluxMPIFluxModel; root_rank::Integer=0)
-    return fmap(y -> FluxMPIB200.synchronize!(y; root_rank), x.model)
+# Walk the wrapped Flux model and hand back the bare model
+# (behaviour of /root/reference/ext/FluxMPIFluxExt.jl:6-8).
+function FluxMPIB200.synchronize!(wrapped::FluxMPIFluxModel; root_rank::Integer=0)
+    each(leaf) = FluxMPIB200.synchronize!(leaf; root_rank=root_rank)
+    return fmap(each, wrapped.model)
 end
 
 end

@@ -28,10 +28,10 @@ export local_rank, total_workers, DistributedOptimizer, fluxmpi_print, fluxmpi_p
 include("abi.jl")        # library handles, enums, struct mirrors, error helpers
 include("host.jl")       # host world: init, barrier, collectives on Arrays
 include("device.jl")     # device world: symmetric segment bring-up, collectives on CuArrays
-include("common.jl")     # Init / ranks / printing
-include("synchronize.jl")
-include("optimizer.jl")
-include("data.jl")
+include("runtime.jl")    # Init / ranks / printing
+include("sync_tree.jl")
+include("dist_optimizer.jl")
+include("sharding.jl")
 
 """
     FluxMPIFluxModel(model)
