@@ -40,6 +40,8 @@ from .parallel.sync import synchronize, synchronize_, FluxMPIFluxModel
 from .parallel.optimizer import DistributedOptimizer, allreduce_gradients
 from .data import DistributedDataContainer, DeviceLoader, TensorDataset
 
+from .utils import checkpoint, trace
+
 __version__ = "0.1.0"
 
 

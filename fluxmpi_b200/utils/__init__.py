@@ -1,0 +1,2 @@
+"""Preferences, checkpointing and tracing helpers."""
+from . import prefs  # noqa: F401

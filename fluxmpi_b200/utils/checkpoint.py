@@ -1,0 +1,74 @@
+"""Checkpoint / resume for data-parallel runs.
+
+The reference has no checkpointing; its guide only says to gate side effects on
+``local_rank() == 0`` (docs/src/guide.md:19) and ``synchronize!`` from ``root_rank`` is the
+building block a user would pair with load-on-root. This module is that pairing:
+
+* ``save(path, tree)`` — rank ``root`` writes (atomically), everyone else waits at a barrier;
+* ``load(path, like=tree)`` — rank ``root`` reads, then the tree is synchronised to all ranks,
+  so a job can resume with a different number of workers;
+* ``save_engine`` / ``load_engine`` — parameters + *full replicated* optimiser state of a
+  :class:`DataParallelEngine` (the owner-sharded moments are gathered first).
+"""
+from __future__ import annotations
+
+import os
+from pathlib import Path
+
+import torch
+
+from .. import runtime
+from .. import tree as T
+from ..parallel.sync import synchronize
+
+
+def _to_cpu(tree):
+    return T.fmap(lambda x: x.detach().cpu() if isinstance(x, torch.Tensor) else x, tree)
+
+
+def save(path, tree, root: int = 0) -> None:
+    """Write ``tree`` (any nested container of tensors / scalars) from rank ``root``."""
+    if runtime.local_rank() == root:
+        p = Path(path)
+        p.parent.mkdir(parents=True, exist_ok=True)
+        tmp = p.with_suffix(p.suffix + f".tmp{os.getpid()}")
+        torch.save(_to_cpu(tree), tmp)
+        os.replace(tmp, p)
+    runtime.host_barrier()
+
+
+def load(path, like, root: int = 0):
+    """Read on ``root``, broadcast into the structure of ``like`` (same shapes) on every rank.
+    Tensors of ``like`` are overwritten in place and the synchronised tree is returned."""
+    if runtime.local_rank() == root:
+        data = torch.load(path, map_location="cpu", weights_only=False)
+
+        def put(dst, src):
+            if isinstance(dst, torch.Tensor):
+                with torch.no_grad():
+                    (dst.detach() if dst.requires_grad else dst).copy_(src)
+                return dst
+            return src
+
+        like = T.fmap2(put, like, data)
+    return synchronize(like, root_rank=root)
+
+
+def save_engine(path, engine, extra=None, root: int = 0) -> None:
+    state = engine.gather_state()                      # collective: every rank takes part
+    payload = {"params": engine.P, "optimizer": state, "steps_done": engine.steps_done,
+               "extra": extra,
+               "buffers": {k: v for k, v in engine.module.named_buffers()}}
+    save(path, payload, root)
+
+
+def load_engine(path, engine, root: int = 0):
+    """Restore parameters, buffers and optimiser state into ``engine`` on every rank."""
+    like = {"params": engine.P, "optimizer": engine.gather_state(), "steps_done": 0, "extra": None,
+            "buffers": {k: v for k, v in engine.module.named_buffers()}}
+    got = load(path, like, root)
+    engine.load_state(got["optimizer"])
+    if engine.master is not None:
+        engine.master.copy_(got["optimizer"].get("master", engine.P.float()))
+    engine.steps_done = int(got["steps_done"])
+    return got["extra"]

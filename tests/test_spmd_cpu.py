@@ -54,6 +54,12 @@ def test_println_rank_order(spmd, tmp_path):
     assert ranks == [0, 1, 2, 3] * 3, ranks
 
 
+def test_checkpoint_roundtrip_and_trace(spmd, tmp_path):
+    """Aux subsystems the reference lacks: checkpoint / resume, tracing."""
+    outs = spmd("checkpoint.py", 3, args=(str(tmp_path / "ckpt.pt"),))
+    assert all(f"RANK_OK {r}" in o for r, o in enumerate(outs))
+
+
 def test_dead_rank_is_detected(spmd):
     """A rank that dies must not leave the others hanging (the reference has no such guard,
     SURVEY §5): the launcher kills the job and reports the failing exit code."""
