@@ -128,7 +128,8 @@ def main():
                 for m, p in zip(master, model.parameters()):
                     m.grad = p.grad.float()
                 opt.step()
-                torch._foreach_copy_(list(model.parameters()), master)
+                with torch.no_grad():
+                    torch._foreach_copy_(list(model.parameters()), master)
             else:
                 opt.step()
             return l
