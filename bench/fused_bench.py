@@ -61,6 +61,10 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default="")
     ap.add_argument("--iters", type=int, default=8)
+    ap.add_argument("--blocks", default="16,48")
+    ap.add_argument("--algos", default="twoshot,nvls")
+    ap.add_argument("--models", default="resnet50,vit_b16,gpt2_medium")
+    ap.add_argument("--no-baseline", action="store_true")
     a = ap.parse_args()
     fm.Init()
     r, w = fm.local_rank(), fm.total_workers()
@@ -73,10 +77,12 @@ def main():
     rows = []
     for name, n, dt in (("resnet50", 25_557_056, torch.float32), ("vit_b16", 86_567_680, torch.float32),
                         ("gpt2_medium", 354_823_168, torch.bfloat16)):
+        if name not in a.models.split(","):
+            continue
         es = 2 if dt == torch.bfloat16 else 4
         row = {"model": name, "numel": n, "dtype": str(dt).split(".")[-1], "world": w}
-        for algo in (["twoshot", "nvls"] if dw.has_multicast and w > 1 else ["twoshot"]):
-            for blocks in ((0,) if w == 1 else (16, 48)):
+        for algo in ([x for x in a.algos.split(",") if x != "nvls" or dw.has_multicast] if w > 1 else ["twoshot"]):
+            for blocks in ((0,) if w == 1 else tuple(int(b) for b in a.blocks.split(","))):
                 mod = Flat(n, dt)
                 eng = DataParallelEngine(mod, R.Adam(1e-3), bucket_mb=1e9, overlap=False, algo=algo,
                                          blocks=blocks, sync_params=False)
@@ -100,13 +106,13 @@ def main():
             if lp is not None:
                 lp.copy_(p.detach())
 
-        row["nccl_plus_fused_adam_us"] = round(timeit(base, lambda: g.normal_(), a.iters, dev), 1)
+        row["nccl_plus_fused_adam_us"] = None if a.no_baseline else round(timeit(base, lambda: g.normal_(), a.iters, dev), 1)
         hbm_owner = (8 * n * es / 4 + 20 * n / w) if dt == torch.float32 else (n * (2 * es + 2) + 24 * n / w)
         row["roofline_p2p_us"] = round(max(hbm_owner / HBM_GBS / 1e3, 2 * (w - 1) / w * n * es / LINK_GBS / 1e3), 1)
         row["roofline_nvls_us"] = round(max(hbm_owner / HBM_GBS / 1e3, n * es / LINK_GBS / 1e3), 1)
         ours = min(v for k, v in row.items() if k.startswith("ours_"))
         row["best_ours_us"] = ours
-        row["speedup_vs_nccl_adam"] = round(row["nccl_plus_fused_adam_us"] / ours, 2)
+        row["speedup_vs_nccl_adam"] = None if a.no_baseline else round(row["nccl_plus_fused_adam_us"] / ours, 2)
         row["fraction_of_roofline"] = round(min(row["roofline_p2p_us"], row["roofline_nvls_us"]) / ours, 3) if w > 1 \
             else round((32 * n / HBM_GBS / 1e3) / ours, 3)
         rows.append(row)

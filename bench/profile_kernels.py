@@ -14,6 +14,7 @@ Also prints CUDA-event timings (the numbers to quote; nothing measured under ncu
 """
 from __future__ import annotations
 
+import os
 import sys
 from pathlib import Path
 
@@ -30,7 +31,12 @@ torch.cuda.set_device(DEV)
 N = 25_557_056            # ResNet-50 parameter count rounded to 64 elements
 
 
-def ev_time(fn, iters=10, warm=3, flush=True):
+ITERS = int(os.environ.get("PROFILE_ITERS", 10))     # PROFILE_ITERS=1 under ncu: one capture per kernel
+
+
+def ev_time(fn, iters=None, warm=None, flush=True):
+    iters = ITERS if iters is None else iters
+    warm = min(3, ITERS) if warm is None else warm
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()

@@ -27,6 +27,7 @@ kernel and the rule is applied with torch ops.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from typing import Callable, Optional
 
@@ -157,8 +158,11 @@ class DataParallelEngine:
         if tuned is not None:
             if algo == "auto":
                 use_nvls = tuned[0] == "nvls" and bool(self.seg.mc_ptr)
-            if blocks == 0 and ((tuned[0] == "nvls") == use_nvls):
-                self.blocks = tuned[1]
+        # CTA count: unlike a pure all-reduce (8-16 CTAs saturate the in-switch path) the fused
+        # kernel also streams m, v and p through HBM; measured at 8 GPUs (bench/fused_bench.py)
+        # 48 CTAs are 1.5-1.9x faster than 16 for both variants, so default well above that
+        if blocks == 0 and self.world > 1:
+            self.blocks = int(os.environ.get("FMPI_FUSED_BLOCKS", 96))
         self.algo = _native.ALGO_NVLS if use_nvls else _native.ALGO_TWOSHOT
 
         # ---- buckets in backward (reverse registration) order
