@@ -230,7 +230,25 @@ class DataParallelEngine:
         self._next = 0
         self._armed = False
 
+    def accumulate(self):
+        """Context manager for gradient accumulation: backward passes inside it only add into
+        the flat gradient buffer (no bucket is launched); the next backward outside it, or
+        :meth:`step`, reduces and applies the accumulated sum."""
+        eng = self
+
+        class _Ctx:
+            def __enter__(self):
+                eng._accumulating = True
+
+            def __exit__(self, *a):
+                eng._accumulating = False
+                eng._reset_buckets()
+
+        return _Ctx()
+
     def _on_grad(self, p):
+        if getattr(self, "_accumulating", False):
+            return
         i = self._bucket_of.get(id(p))
         if i is None:
             return

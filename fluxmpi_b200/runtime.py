@@ -24,6 +24,7 @@ from __future__ import annotations
 import atexit
 import ctypes as C
 import datetime as _dt
+import logging
 import os
 import sys
 import threading
@@ -64,6 +65,7 @@ class _State:
 
 
 _S = _State()
+_log = logging.getLogger("fluxmpi_b200")
 
 # ---------------------------------------------------------------------------- configuration
 
@@ -165,6 +167,16 @@ def Init(gpu_devices: Optional[Sequence[int]] = None, verbose: bool = False,
             rank=rank, world=world, device=dev, job=_S.job, disabled=_S.p2p_disabled,
             window_bytes=device_window_bytes, verbose=verbose)
         _S.topology = _S.device_world.topology
+        # one capability message per process, like the reference's load-time probe
+        # (src/FluxMPI.jl:25-31: "CUDA-aware MPI support disabled" / "not CUDA Aware" / "is CUDA Aware")
+        dw = _S.device_world
+        if _S.p2p_disabled and world > 1:
+            _log.info("NVLink P2P support disabled using LocalPreferences.toml; device collectives use NCCL.")
+        elif world > 1 and not dw.native:
+            _log.warning("NVLink peer-to-peer memory is not available (%s); device collectives use NCCL.",
+                         dw.why_fallback)
+        else:
+            _log.info("NVLink P2P kernels active (mode=%s, multicast=%s).", dw.mode, dw.has_multicast)
     else:
         _S.device = torch.device("cpu")
         if verbose:

@@ -208,3 +208,37 @@ def test_launcher_propagates_exit_code(tmp_path):
     s.write_text("import os, sys, time\nif os.environ['RANK']=='1': sys.exit(7)\ntime.sleep(60)\n")
     code, _ = launch(3, [str(s)], timeout=30, capture=True)
     assert code == 7
+
+
+# ------------------------------------------------------------------------------ tuner
+def test_tuner_lookup(tmp_path, monkeypatch):
+    import json
+    from fluxmpi_b200.parallel.tuner import Tuner
+    f = tmp_path / "tuned.json"
+    f.write_text(json.dumps({"4": {"allreduce_any": [
+        {"bytes": 1 << 20, "algo": "twoshot", "blocks": 32, "threads": 256},
+        {"bytes": 64 << 20, "algo": "nvls", "blocks": 148, "threads": 512}]}}))
+    t = Tuner(4, True, str(f))
+    assert t.choice("allreduce_any", 2 << 20) == ("twoshot", 32, 256)       # nearest on a log scale
+    assert t.choice("allreduce_any", 100 << 20) == ("nvls", 148, 512)
+    assert t.choice("allreduce_any", 1000) is None                          # below the measured range
+    assert t.choice("bcast_any", 1 << 20) is None                           # no table for this op
+    ref, obj = t.launch("allreduce_any", 3 << 20)
+    assert (obj.blocks, obj.threads, obj.algo) == (32, 256, 2)
+    assert t.launch("allreduce_any", 3 << 20)[1] is obj                     # cached per size bucket
+    no_mc = Tuner(4, False, str(f))
+    assert no_mc.choice("allreduce_any", 100 << 20) == ("twoshot", 32, 256)  # nvls rows dropped
+    assert Tuner(8, True, str(f)).choice("allreduce_any", 1 << 20) is None
+    monkeypatch.setenv("FMPI_NO_TUNE", "1")
+    assert Tuner(4, True, str(f)).choice("allreduce_any", 2 << 20) is None
+
+
+def test_shipped_tuned_table_is_well_formed():
+    import json
+    from pathlib import Path
+    import fluxmpi_b200.parallel.tuner as tuner_mod
+    data = json.loads(Path(tuner_mod.__file__).with_name("tuned.json").read_text())
+    for world in ("2", "4", "8"):
+        for op in ("allreduce_any", "reduce_any", "bcast_any", "allreduce_symm", "bcast_symm"):
+            rows = data[world][op]
+            assert rows and all(r["algo"] in ("oneshot", "twoshot", "nvls") and 1 <= r["blocks"] <= 160 for r in rows)
