@@ -148,3 +148,103 @@ def flush_l2(device=None, nbytes: int = 256 << 20):
         buf = torch.empty(nbytes, dtype=torch.uint8, device=device)
         _flush_buf[device] = buf
     cuda_check(_native.cuda().fmpi_flush_l2(buf.data_ptr(), nbytes, _stream_ptr()), "flush_l2")
+
+
+# ------------------------------------------------------------------------------ functional trees
+_table_cache: dict = {}
+
+
+def _rule_state_tensors(rule, state):
+    """(m, v, step, rebuild) for a fusable rule's per-leaf state, or None if the layout is not
+    the one ``rule.init`` produces. ``rebuild(step+1)`` returns the state to store back."""
+    import math
+    r, _ = unwrap_rule(rule)
+    if type(r) is R.Descent:
+        return None, None, 0, (lambda: state)
+    if type(r) in (R.Momentum, R.Nesterov):
+        if not isinstance(state, torch.Tensor):
+            return None
+        return state, None, 0, (lambda: state)
+    if type(r) is R.Adam:
+        adam, st, wrap = r, state, (lambda s: s)
+    elif type(r) is R.OptimiserChain and len(r.opts) == 2 and type(r.opts[0]) is R.Adam:
+        adam, st, wrap = r.opts[0], state[0], (lambda s: (s, state[1]))
+    else:
+        return None
+    if not (isinstance(st, tuple) and len(st) == 3 and isinstance(st[0], torch.Tensor)):
+        return None
+    mt, vt, bt = st
+    b1 = adam.beta[0]
+    step = int(round(math.log(bt[0]) / math.log(b1))) - 1 if 0 < b1 < 1 else 0
+    return mt, vt, max(step, 0), (lambda: wrap((mt, vt, (bt[0] * adam.beta[0], bt[1] * adam.beta[1]))))
+
+
+def try_tree_step_(state_tree, params, grads) -> bool:
+    """One-kernel in-place optimiser step for a whole tree of CUDA leaves
+    (``Optimisers.update!`` semantics): returns False — having changed nothing — when any leaf
+    does not qualify (mixed rules or dtypes, CPU tensors, non-contiguous storage, fp64, a rule
+    without a fused kernel); the caller then walks the tree leaf by leaf."""
+    from .. import tree as T
+    triples, seen = [], set()
+
+    def walk(st, p, g) -> bool:
+        if isinstance(st, R.Leaf):
+            if g is None or st.frozen:
+                return True
+            if id(p) in seen:
+                return True
+            seen.add(id(p))
+            triples.append((st, p, g))
+            return True
+        if st is None or not T.is_container(st):
+            return True
+        cs = [c for _, c in T.children(st)]
+        cp = [c for _, c in T.children(p)]
+        cg = [c for _, c in T.children(g)] if g is not None and T.is_container(g) else [None] * len(cs)
+        if not (len(cs) == len(cp) == len(cg)):
+            return False
+        return all(walk(a, b, c) for a, b, c in zip(cs, cp, cg))
+
+    if not walk(state_tree, params, grads) or not triples:
+        return False
+    rule = triples[0][0].rule
+    h = hyper_for(rule)
+    if h is None:
+        return False
+    dt = triples[0][1].dtype
+    if dt not in (torch.float32, torch.bfloat16, torch.float16):
+        return False
+    ms, vs, ps, gs, rebuilds, step = [], [], [], [], [], None
+    for leaf, p, g in triples:
+        if leaf.rule != rule or not (isinstance(p, torch.Tensor) and isinstance(g, torch.Tensor)):
+            return False
+        pd, gd = (p.detach() if p.requires_grad else p), (g.detach() if g.requires_grad else g)
+        if not (pd.is_cuda and gd.is_cuda and pd.dtype == dt and gd.dtype == dt and pd.is_contiguous()
+                and gd.is_contiguous() and pd.shape == gd.shape and pd.numel() > 0):
+            return False
+        got = _rule_state_tensors(rule, leaf.state)
+        if got is None:
+            return False
+        m, v, s, rebuild = got
+        for t in (m, v):
+            if t is not None and not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()
+                                      and t.shape == pd.shape):
+                return False
+        if step is None:
+            step = s
+        elif s != step:
+            return False
+        ps.append(pd); gs.append(gd); ms.append(m); vs.append(v); rebuilds.append(rebuild)
+    need_m, need_v = rule_needs(h)
+    key = tuple(t.data_ptr() for t in ps + gs) + tuple(t.data_ptr() for t in ms + vs if t is not None)
+    table = _table_cache.get(key)
+    if table is None:
+        if len(_table_cache) > 16:
+            _table_cache.clear()
+        table = TensorTable(ps, gs, ms if need_m else None, vs if need_v else None)
+        _table_cache[key] = table
+    # (averaging, if asked for, has already been applied to the gradients by the caller)
+    multi_tensor_step(table, h, step or 0, dt)
+    for (leaf, _, _), rebuild in zip(triples, rebuilds):
+        leaf.state = rebuild()
+    return True

@@ -378,12 +378,25 @@ def update_(state_tree, params, grads):
     hook = getattr(_first_rule(state_tree), "tree_update", None)
     if hook is not None:
         return hook(state_tree, params, grads, True)
-    return _walk_update(state_tree, params, grads, True, {})
+    return walk_update(state_tree, params, grads, True)
 
 
 def walk_update(state_tree, params, grads, inplace: bool):
-    """The plain per-leaf walk (for rules that implement ``tree_update``)."""
+    """The per-leaf walk (for rules that implement ``tree_update``). An in-place step over a
+    tree of CUDA leaves with a fusable rule is ONE pointer-table kernel launch
+    (ops/fused.py, csrc/kernels/multi_tensor.cu) instead of 2-4 elementwise kernels per leaf."""
+    if inplace and _any_cuda(params):
+        from .ops import fused
+        if fused.try_tree_step_(state_tree, params, grads):
+            return state_tree, params
     return _walk_update(state_tree, params, grads, inplace, {})
+
+
+def _any_cuda(params) -> bool:
+    for x in T.leaves(params):
+        if isinstance(x, torch.Tensor):
+            return x.is_cuda
+    return False
 
 
 def _first_rule(state_tree):

@@ -32,7 +32,7 @@ def _train_reference(model, opt, batches, loss_fn):
         loss = loss_fn(model(x), y)
         loss.backward()
         opt.step()
-        losses.append(float(loss))
+        losses.append(float(loss.detach()))
     return losses
 
 
@@ -62,7 +62,7 @@ def test_engine_matches_torch_optim(rule, topt):
         loss = loss_fn(ours(x), y)
         loss.backward()
         eng.step()
-        losses.append(float(loss))
+        losses.append(float(loss.detach()))
     assert _native.launch_count - before >= 2 * len(batches)      # fused step + step counter
     assert torch.allclose(torch.tensor(losses), torch.tensor(ref_losses), rtol=2e-3, atol=2e-3), (losses, ref_losses)
     for (n, a), (_, b) in zip(ours.named_parameters(), ref.named_parameters()):
@@ -183,6 +183,38 @@ def test_functional_api_on_device_tensors():
     assert out["b"][2] == 1.5 and out["a"] is tree["a"]
     gs = fm.allreduce_gradients({"a": torch.ones(4, device="cuda"), "b": torch.ones(4, device="cuda")})
     assert torch.equal(gs["a"], torch.ones(4, device="cuda"))
+
+
+@pytest.mark.parametrize("rule", [R.Adam(1e-2), R.AdamW(1e-2, (0.9, 0.99), 1e-3), R.Momentum(0.05, 0.9),
+                                  R.Nesterov(0.05, 0.9), R.Descent(0.1)],
+                         ids=["Adam", "AdamW", "Momentum", "Nesterov", "Descent"])
+def test_functional_update_inplace_is_one_fused_launch(rule):
+    """rules.update_ on a tree of CUDA leaves (Optimisers.update! shape) takes the pointer-table
+    kernel: same numbers as the leaf-by-leaf torch path, one launch per step."""
+    g = torch.Generator().manual_seed(4)
+    mk = lambda: {"l1": {"w": torch.randn(17, 5, generator=g).cuda(), "b": torch.randn(5, generator=g).cuda()},
+                  "l2": (torch.randn(4099, generator=g).cuda(), None, "tag")}
+    ps = mk()
+    ref_ps = fm.fmap(lambda t: t.clone() if isinstance(t, torch.Tensor) else t, ps)
+    drule = fm.DistributedOptimizer(rule)
+    st, ref_st = R.setup(drule, ps), R.setup(rule, ref_ps)
+    for step in range(3):
+        gs = fm.fmap(lambda t: torch.randn(t.shape, generator=g).cuda() if isinstance(t, torch.Tensor) else t, ps)
+        before = _native.launch_count
+        st, ps2 = R.update_(st, ps, gs)
+        assert ps2["l1"]["w"] is ps["l1"]["w"]
+        assert _native.launch_count - before == 1, "expected exactly one multi-tensor launch"
+        ref_st, ref_ps = R.update(ref_st, ref_ps, gs)
+    for a, b in ((ps["l1"]["w"], ref_ps["l1"]["w"]), (ps["l1"]["b"], ref_ps["l1"]["b"]), (ps["l2"][0], ref_ps["l2"][0])):
+        assert torch.allclose(a, b, rtol=2e-5, atol=2e-6)
+    if isinstance(rule, R.Adam):
+        assert abs(st["l1"]["w"].state[2][0] - 0.9 ** 4) < 1e-12       # β-powers keep Optimisers' bookkeeping
+        assert torch.allclose(st["l1"]["w"].state[0], ref_st["l1"]["w"].state[0], rtol=1e-5, atol=1e-7)
+    # a rule without a kernel still works through the torch path
+    st2 = R.setup(R.RMSProp(1e-3), ps)
+    before = _native.launch_count
+    R.update_(st2, ps, gs)
+    assert _native.launch_count == before
 
 
 def test_device_loader_pinned_double_buffered():
