@@ -47,6 +47,8 @@ def parse():
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-overlap", action="store_true")
+    ap.add_argument("--no-fused-bn", action="store_true",
+                    help="ours: use stock nn.BatchNorm2d + ReLU instead of the fused channels-last kernels")
     ap.add_argument("--bucket-mb", type=float, default=32.0)
     ap.add_argument("--algo", default="auto")
     return ap.parse_args()
@@ -104,9 +106,12 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------ shared pieces
-def make_model(name):
+def make_model(name, fused_bn=False):
+    """Same architecture, parameters and initialisation in both arms. ``fused_bn`` swaps the
+    BatchNorm2d / ReLU / residual-add modules for the framework's channels-last kernels (our
+    arm); the DDP arm always runs the stock PyTorch modules."""
     from fluxmpi_b200.models import resnet50, resnet_tiny
-    return resnet50() if name == "resnet50" else resnet_tiny(1000)
+    return resnet50(fused_bn=fused_bn) if name == "resnet50" else resnet_tiny(1000, fused_bn=fused_bn)
 
 
 def host_dataset(n_batches: int, batch: int, image: int, seed: int):
@@ -202,7 +207,7 @@ def run_ours(a):
     cdt = torch.bfloat16 if a.dtype == "bf16" else torch.float32
 
     torch.manual_seed(rank)
-    model = make_model(a.model).to(dev).to(memory_format=torch.channels_last)
+    model = make_model(a.model, fused_bn=not a.no_fused_bn).to(dev).to(memory_format=torch.channels_last)
     engine = DataParallelEngine(model, fm.DistributedOptimizer(R.Adam(1e-3)), bucket_mb=a.bucket_mb,
                                 overlap=not a.no_overlap, algo=a.algo)
     inv_w = 1.0 / world                        # reference semantics: SUM, loss scaled by 1/W
@@ -302,6 +307,7 @@ def run_ours(a):
             "config": {"model": a.model, "global_batch": gb, "per_gpu_batch": a.batch, "image": a.image,
                        "seq_len": None, "parallelism": f"dp{world}", "optimizer": "Adam(1e-3), fused with the gradient all-reduce",
                        "layout": "channels_last", "cuda_graph": not a.no_graph, "overlap": not a.no_overlap,
+                       "batchnorm": "stock nn.BatchNorm2d" if a.no_fused_bn else "fused channels-last BN(+add)(+ReLU) kernels (ours)",
                        "bucket_mb": a.bucket_mb, "buckets": len(engine.buckets),
                        "comm": f"{dw.mode}{'+nvls' if engine.algo == _native.ALGO_NVLS else ''}",
                        "l2": "per-step working set (activations of 256 images + 205 MB of parameters and gradients) far exceeds the 126 MB L2; no explicit flush",

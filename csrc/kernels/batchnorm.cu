@@ -1,0 +1,484 @@
+// Channels-last batch normalisation (training) fused with the residual add and the ReLU that
+// follow it in ResNet bottlenecks — forward and backward, bf16 / f16 / f32 I/O, fp32 math.
+//
+// Why this is in a data-parallel library: measured with `ncu --metrics gpu__time_duration`
+// (profiles/README.md §7), PyTorch's native channels_last batch-norm kernels are 60.7 % of the
+// GPU time of a ResNet-50 training step on B200 and the separate ReLU / add kernels another
+// 15 %, while the convolutions are 19 %. The headline benchmark (BASELINE.json config 2) is
+// therefore bound by memory-bound normalisation code that runs far from the HBM roofline, and
+// that is exactly the kind of op to hand-write (the reference has no model code at all; its
+// users get whatever Lux/Flux + cuDNN give them).
+//
+// Layout: x is [M, C] row-major (M = N*H*W rows, C channels; that is NHWC memory). A CTA is a
+// (tx channel-vectors) x (ty row-lanes) tile of 256 threads; a thread owns one 16-byte channel
+// vector (8 bf16 or 4 f32 channels), keeps that vector's per-channel constants in registers
+// and walks down the rows with four 16-byte loads in flight. Column reductions (statistics,
+// d_gamma / d_beta) are per-thread fp32 partials -> shared-memory tree over the row-lanes ->
+// one partial per CTA in scratch -> a tiny finalize kernel that folds them in double.
+//
+//   forward : stats -> finalize (mean, invstd, scale, shift, running stats) -> apply
+//             y = relu?(x * scale + shift (+ residual))
+//   backward: reduce (sum dz, sum dz*xhat; dz = dy * (y > 0) when ReLU is fused) -> finalize
+//             (d_beta, d_gamma, coefficients) -> apply dx = a * (dz - b1 - xhat * b2), d_res = dz
+#include "common.cuh"
+
+namespace fmpi {
+
+struct BNGeom {
+  int tx, ty, gy;
+  unsigned gx;
+  uint64_t rows_per_cta;
+};
+
+constexpr int kBNThreads = 256;
+constexpr int kBNMaxGx = 1024;
+
+__host__ inline BNGeom bn_geom(uint64_t M, int VC) {
+  BNGeom g;
+  g.tx = 1;
+  while (g.tx < 32 && g.tx * 2 <= VC) g.tx *= 2;
+  g.ty = kBNThreads / g.tx;
+  g.gy = (VC + g.tx - 1) / g.tx;
+  uint64_t want = (148ull * 8 + g.gy - 1) / g.gy;
+  const uint64_t max_gx = (M + g.ty - 1) / g.ty;
+  if (want > max_gx) want = max_gx;
+  if (want > kBNMaxGx) want = kBNMaxGx;
+  if (want < 1) want = 1;
+  uint64_t rows = (M + want - 1) / want;
+  rows = (rows + g.ty - 1) / g.ty * g.ty;
+  g.rows_per_cta = rows;
+  g.gx = unsigned((M + rows - 1) / rows);
+  return g;
+}
+
+struct BNIdx {
+  int cx, ry, vc;
+  bool act;
+  uint64_t r0, r1;
+};
+
+template <int N>
+__device__ __forceinline__ BNIdx bn_idx(uint64_t M, int C, int tx, uint64_t rows_per_cta) {
+  BNIdx i;
+  i.cx = threadIdx.x % tx;
+  i.ry = threadIdx.x / tx;
+  i.vc = blockIdx.y * tx + i.cx;
+  i.act = i.vc * N < C;
+  i.r0 = uint64_t(blockIdx.x) * rows_per_cta;
+  i.r1 = min(i.r0 + rows_per_cta, M);
+  return i;
+}
+
+template <int N>
+__device__ __forceinline__ void load_consts(const float* __restrict__ p, int c0, float* out) {
+#pragma unroll
+  for (int k = 0; k < N; k += 4) *reinterpret_cast<float4*>(out + k) = *reinterpret_cast<const float4*>(p + c0 + k);
+}
+
+// Tree-reduce K floats per thread over the row-lanes (ry) of the CTA; result valid where ry == 0.
+template <int K>
+__device__ __forceinline__ void lanes_reduce(float* v, float* sm, int tx, int ty, int cx, int ry) {
+  float* mine = sm + (size_t(ry) * tx + cx) * K;
+#pragma unroll
+  for (int k = 0; k < K; ++k) mine[k] = v[k];
+  __syncthreads();
+  for (int off = ty >> 1; off > 0; off >>= 1) {
+    if (ry < off) {
+      const float* other = sm + (size_t(ry + off) * tx + cx) * K;
+#pragma unroll
+      for (int k = 0; k < K; ++k) mine[k] += other[k];
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int k = 0; k < K; ++k) v[k] = mine[k];
+}
+
+// ---------------------------------------------------------------------------- forward
+template <typename T>
+__global__ void __launch_bounds__(kBNThreads)
+bn_stats_kernel(const T* __restrict__ x, uint64_t M, int C, int tx, uint64_t rows_per_cta, float* __restrict__ partial) {
+  using V = VecOps<T>;
+  constexpr int N = V::kN;
+  extern __shared__ float sm[];
+  const int ty = blockDim.x / tx;
+  const BNIdx i = bn_idx<N>(M, C, tx, rows_per_cta);
+  float acc[2 * N];
+#pragma unroll
+  for (int k = 0; k < 2 * N; ++k) acc[k] = 0.f;
+  if (i.act) {
+    const uint8_t* base = reinterpret_cast<const uint8_t*>(x) + uint64_t(i.vc) * 16;
+    const uint64_t rb = uint64_t(C) * sizeof(T);
+    for (uint64_t r = i.r0 + i.ry; r < i.r1; r += 4ull * ty) {
+      uint4 raw[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (r + uint64_t(u) * ty < i.r1) raw[u] = ld_stream(base + (r + uint64_t(u) * ty) * rb);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (r + uint64_t(u) * ty < i.r1) {
+          float e[N];
+          V::unpack(raw[u], e);
+#pragma unroll
+          for (int k = 0; k < N; ++k) {
+            acc[k] += e[k];
+            acc[N + k] += e[k] * e[k];
+          }
+        }
+    }
+  }
+  lanes_reduce<2 * N>(acc, sm, tx, ty, i.cx, i.ry);
+  if (i.ry == 0 && i.act) {
+    float* p = partial + uint64_t(blockIdx.x) * 2 * C + i.vc * N;
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+      p[k] = acc[k];
+      p[C + k] = acc[N + k];
+    }
+  }
+}
+
+__global__ void bn_fwd_finalize_kernel(const float* __restrict__ partial, unsigned gx, uint64_t M, int C,
+                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                       float* running_mean, float* running_var, float momentum, float eps,
+                                       float* save_mean, float* save_invstd, float* scale, float* shift) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s = 0.0, q = 0.0;
+  for (unsigned g = 0; g < gx; ++g) {
+    s += double(partial[uint64_t(g) * 2 * C + c]);
+    q += double(partial[uint64_t(g) * 2 * C + C + c]);
+  }
+  const double mean = s / double(M);
+  double var = q / double(M) - mean * mean;
+  if (var < 0.0) var = 0.0;
+  const float invstd = float(1.0 / sqrt(var + double(eps)));
+  save_mean[c] = float(mean);
+  save_invstd[c] = invstd;
+  const float sc = (gamma ? gamma[c] : 1.f) * invstd;
+  scale[c] = sc;
+  shift[c] = (beta ? beta[c] : 0.f) - float(mean) * sc;
+  if (running_mean) running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * float(mean);
+  if (running_var) {
+    const double unbiased = M > 1 ? var * double(M) / double(M - 1) : var;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * float(unbiased);
+  }
+}
+
+template <typename T, bool kRelu, bool kRes>
+__global__ void __launch_bounds__(kBNThreads)
+bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restrict__ y, uint64_t M, int C, int tx,
+                uint64_t rows_per_cta, const float* __restrict__ scale, const float* __restrict__ shift) {
+  using V = VecOps<T>;
+  constexpr int N = V::kN;
+  const int ty = blockDim.x / tx;
+  const BNIdx i = bn_idx<N>(M, C, tx, rows_per_cta);
+  if (!i.act) return;
+  float sc[N], sh[N];
+  load_consts<N>(scale, i.vc * N, sc);
+  load_consts<N>(shift, i.vc * N, sh);
+  const uint64_t rb = uint64_t(C) * sizeof(T);
+  const uint64_t col = uint64_t(i.vc) * 16;
+  const uint8_t* xb = reinterpret_cast<const uint8_t*>(x) + col;
+  const uint8_t* rbp = kRes ? reinterpret_cast<const uint8_t*>(res) + col : nullptr;
+  uint8_t* yb = reinterpret_cast<uint8_t*>(y) + col;
+  for (uint64_t r = i.r0 + i.ry; r < i.r1; r += 4ull * ty) {
+    uint4 xr[4], rr[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (r + uint64_t(u) * ty < i.r1) {
+        xr[u] = ld_stream(xb + (r + uint64_t(u) * ty) * rb);
+        if (kRes) rr[u] = ld_stream(rbp + (r + uint64_t(u) * ty) * rb);
+      }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (r + uint64_t(u) * ty < i.r1) {
+        float e[N], z[N];
+        V::unpack(xr[u], e);
+        if (kRes) V::unpack(rr[u], z);
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          float o = e[k] * sc[k] + sh[k];
+          if (kRes) o += z[k];
+          if (kRelu) o = fmaxf(o, 0.f);
+          e[k] = o;
+        }
+        *reinterpret_cast<uint4*>(yb + (r + uint64_t(u) * ty) * rb) = V::pack(e);
+      }
+  }
+}
+
+// ---------------------------------------------------------------------------- backward
+template <typename T, bool kRelu>
+__global__ void __launch_bounds__(kBNThreads)
+bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x, uint64_t M, int C,
+                     int tx, uint64_t rows_per_cta, const float* __restrict__ mean,
+                     const float* __restrict__ invstd, float* __restrict__ partial) {
+  using V = VecOps<T>;
+  constexpr int N = V::kN;
+  extern __shared__ float sm[];
+  const int ty = blockDim.x / tx;
+  const BNIdx i = bn_idx<N>(M, C, tx, rows_per_cta);
+  float acc[2 * N];
+#pragma unroll
+  for (int k = 0; k < 2 * N; ++k) acc[k] = 0.f;
+  if (i.act) {
+    float mu[N], is[N];
+    load_consts<N>(mean, i.vc * N, mu);
+    load_consts<N>(invstd, i.vc * N, is);
+    const uint64_t rb = uint64_t(C) * sizeof(T);
+    const uint64_t col = uint64_t(i.vc) * 16;
+    const uint8_t* db = reinterpret_cast<const uint8_t*>(dy) + col;
+    const uint8_t* yb = kRelu ? reinterpret_cast<const uint8_t*>(y) + col : nullptr;
+    const uint8_t* xb = reinterpret_cast<const uint8_t*>(x) + col;
+    for (uint64_t r = i.r0 + i.ry; r < i.r1; r += 2ull * ty) {
+      uint4 dr[2], yr[2], xr[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u)
+        if (r + uint64_t(u) * ty < i.r1) {
+          const uint64_t o = (r + uint64_t(u) * ty) * rb;
+          dr[u] = ld_stream(db + o);
+          xr[u] = ld_stream(xb + o);
+          if (kRelu) yr[u] = ld_stream(yb + o);
+        }
+#pragma unroll
+      for (int u = 0; u < 2; ++u)
+        if (r + uint64_t(u) * ty < i.r1) {
+          float d[N], xe[N], ye[N];
+          V::unpack(dr[u], d);
+          V::unpack(xr[u], xe);
+          if (kRelu) V::unpack(yr[u], ye);
+#pragma unroll
+          for (int k = 0; k < N; ++k) {
+            const float dz = (kRelu && !(ye[k] > 0.f)) ? 0.f : d[k];
+            acc[k] += dz;
+            acc[N + k] += dz * (xe[k] - mu[k]) * is[k];
+          }
+        }
+    }
+  }
+  lanes_reduce<2 * N>(acc, sm, tx, ty, i.cx, i.ry);
+  if (i.ry == 0 && i.act) {
+    float* p = partial + uint64_t(blockIdx.x) * 2 * C + i.vc * N;
+#pragma unroll
+    for (int k = 0; k < N; ++k) {
+      p[k] = acc[k];
+      p[C + k] = acc[N + k];
+    }
+  }
+}
+
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, unsigned gx, uint64_t M, int C,
+                                       const float* __restrict__ gamma, const float* __restrict__ invstd,
+                                       float* dgamma, float* dbeta, float* a, float* b1, float* b2) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  double s1 = 0.0, s2 = 0.0;
+  for (unsigned g = 0; g < gx; ++g) {
+    s1 += double(partial[uint64_t(g) * 2 * C + c]);
+    s2 += double(partial[uint64_t(g) * 2 * C + C + c]);
+  }
+  if (dbeta) dbeta[c] = float(s1);
+  if (dgamma) dgamma[c] = float(s2);
+  a[c] = (gamma ? gamma[c] : 1.f) * invstd[c];
+  b1[c] = float(s1 / double(M));
+  b2[c] = float(s2 / double(M));
+}
+
+template <typename T, bool kRelu, bool kRes>
+__global__ void __launch_bounds__(kBNThreads)
+bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x, T* __restrict__ dx,
+                    T* __restrict__ dres, uint64_t M, int C, int tx, uint64_t rows_per_cta,
+                    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ a,
+                    const float* __restrict__ b1, const float* __restrict__ b2) {
+  using V = VecOps<T>;
+  constexpr int N = V::kN;
+  const int ty = blockDim.x / tx;
+  const BNIdx i = bn_idx<N>(M, C, tx, rows_per_cta);
+  if (!i.act) return;
+  float mu[N], is[N], ca[N], c1[N], c2[N];
+  load_consts<N>(mean, i.vc * N, mu);
+  load_consts<N>(invstd, i.vc * N, is);
+  load_consts<N>(a, i.vc * N, ca);
+  load_consts<N>(b1, i.vc * N, c1);
+  load_consts<N>(b2, i.vc * N, c2);
+  const uint64_t rb = uint64_t(C) * sizeof(T);
+  const uint64_t col = uint64_t(i.vc) * 16;
+  const uint8_t* db = reinterpret_cast<const uint8_t*>(dy) + col;
+  const uint8_t* yb = kRelu ? reinterpret_cast<const uint8_t*>(y) + col : nullptr;
+  const uint8_t* xb = reinterpret_cast<const uint8_t*>(x) + col;
+  uint8_t* ob = reinterpret_cast<uint8_t*>(dx) + col;
+  uint8_t* rbp = kRes ? reinterpret_cast<uint8_t*>(dres) + col : nullptr;
+  for (uint64_t r = i.r0 + i.ry; r < i.r1; r += 2ull * ty) {
+    uint4 dr[2], yr[2], xr[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
+      if (r + uint64_t(u) * ty < i.r1) {
+        const uint64_t o = (r + uint64_t(u) * ty) * rb;
+        dr[u] = ld_stream(db + o);
+        xr[u] = ld_stream(xb + o);
+        if (kRelu) yr[u] = ld_stream(yb + o);
+      }
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
+      if (r + uint64_t(u) * ty < i.r1) {
+        const uint64_t o = (r + uint64_t(u) * ty) * rb;
+        float d[N], xe[N], ye[N], g[N];
+        V::unpack(dr[u], d);
+        V::unpack(xr[u], xe);
+        if (kRelu) V::unpack(yr[u], ye);
+#pragma unroll
+        for (int k = 0; k < N; ++k) {
+          const float dz = (kRelu && !(ye[k] > 0.f)) ? 0.f : d[k];
+          d[k] = dz;
+          const float xh = (xe[k] - mu[k]) * is[k];
+          g[k] = ca[k] * (dz - c1[k] - xh * c2[k]);
+        }
+        *reinterpret_cast<uint4*>(ob + o) = V::pack(g);
+        if (kRes) *reinterpret_cast<uint4*>(rbp + o) = V::pack(d);
+      }
+  }
+}
+
+}  // namespace fmpi
+
+using namespace fmpi;
+using fmpi_host::check_cuda;
+using fmpi_host::set_error;
+
+namespace {
+
+// scratch (floats): partial[kBNMaxGx][2][C] | scale | shift | a | b1 | b2
+size_t bn_scratch_floats(int C) { return size_t(kBNMaxGx) * 2 * C + 5 * size_t(C); }
+
+template <typename T>
+int bn_forward_t(const void* x, const void* res, void* y, uint64_t M, int C, const float* gamma, const float* beta,
+                 float* rmean, float* rvar, float momentum, float eps, int relu, float* save_mean,
+                 float* save_invstd, float* scratch, cudaStream_t st) {
+  constexpr int N = VecOps<T>::kN;
+  const BNGeom g = bn_geom(M, C / N);
+  float* partial = scratch;
+  float* scale = scratch + size_t(kBNMaxGx) * 2 * C;
+  float* shift = scale + C;
+  const dim3 grid(g.gx, g.gy);
+  const size_t smem = size_t(kBNThreads) * 2 * N * sizeof(float);
+  bn_stats_kernel<T><<<grid, kBNThreads, smem, st>>>(static_cast<const T*>(x), M, C, g.tx, g.rows_per_cta, partial);
+  bn_fwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, g.gx, M, C, gamma, beta, rmean, rvar, momentum,
+                                                          eps, save_mean, save_invstd, scale, shift);
+  const T* xp = static_cast<const T*>(x);
+  const T* rp = static_cast<const T*>(res);
+  T* yp = static_cast<T*>(y);
+  if (relu) {
+    if (res) bn_apply_kernel<T, true, true><<<grid, kBNThreads, 0, st>>>(xp, rp, yp, M, C, g.tx, g.rows_per_cta, scale, shift);
+    else bn_apply_kernel<T, true, false><<<grid, kBNThreads, 0, st>>>(xp, rp, yp, M, C, g.tx, g.rows_per_cta, scale, shift);
+  } else {
+    if (res) bn_apply_kernel<T, false, true><<<grid, kBNThreads, 0, st>>>(xp, rp, yp, M, C, g.tx, g.rows_per_cta, scale, shift);
+    else bn_apply_kernel<T, false, false><<<grid, kBNThreads, 0, st>>>(xp, rp, yp, M, C, g.tx, g.rows_per_cta, scale, shift);
+  }
+  return check_cuda(cudaGetLastError(), "bn_forward launch");
+}
+
+template <typename T>
+int bn_apply_t(const void* x, const void* res, void* y, uint64_t M, int C, const float* scale, const float* shift,
+               int relu, cudaStream_t st) {
+  constexpr int N = VecOps<T>::kN;
+  const BNGeom g = bn_geom(M, C / N);
+  const dim3 grid(g.gx, g.gy);
+  const T* xp = static_cast<const T*>(x);
+  const T* rp = static_cast<const T*>(res);
+  T* yp = static_cast<T*>(y);
+  if (relu) {
+    if (res) bn_apply_kernel<T, true, true><<<grid, kBNThreads, 0, st>>>(xp, rp, yp, M, C, g.tx, g.rows_per_cta, scale, shift);
+    else bn_apply_kernel<T, true, false><<<grid, kBNThreads, 0, st>>>(xp, rp, yp, M, C, g.tx, g.rows_per_cta, scale, shift);
+  } else {
+    if (res) bn_apply_kernel<T, false, true><<<grid, kBNThreads, 0, st>>>(xp, rp, yp, M, C, g.tx, g.rows_per_cta, scale, shift);
+    else bn_apply_kernel<T, false, false><<<grid, kBNThreads, 0, st>>>(xp, rp, yp, M, C, g.tx, g.rows_per_cta, scale, shift);
+  }
+  return check_cuda(cudaGetLastError(), "bn_apply launch");
+}
+
+template <typename T>
+int bn_backward_t(const void* dy, const void* y, const void* x, void* dx, void* dres, uint64_t M, int C,
+                  const float* gamma, const float* mean, const float* invstd, float* dgamma, float* dbeta, int relu,
+                  float* scratch, cudaStream_t st) {
+  constexpr int N = VecOps<T>::kN;
+  const BNGeom g = bn_geom(M, C / N);
+  float* partial = scratch;
+  float* a = scratch + size_t(kBNMaxGx) * 2 * C + 2 * size_t(C);
+  float* b1 = a + C;
+  float* b2 = b1 + C;
+  const dim3 grid(g.gx, g.gy);
+  const size_t smem = size_t(kBNThreads) * 2 * N * sizeof(float);
+  const T* dp = static_cast<const T*>(dy);
+  const T* yp = static_cast<const T*>(y);
+  const T* xp = static_cast<const T*>(x);
+  T* op = static_cast<T*>(dx);
+  T* rp = static_cast<T*>(dres);
+  if (relu) bn_bwd_reduce_kernel<T, true><<<grid, kBNThreads, smem, st>>>(dp, yp, xp, M, C, g.tx, g.rows_per_cta, mean, invstd, partial);
+  else bn_bwd_reduce_kernel<T, false><<<grid, kBNThreads, smem, st>>>(dp, yp, xp, M, C, g.tx, g.rows_per_cta, mean, invstd, partial);
+  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, g.gx, M, C, gamma, invstd, dgamma, dbeta, a, b1, b2);
+  if (relu) {
+    if (dres) bn_bwd_apply_kernel<T, true, true><<<grid, kBNThreads, 0, st>>>(dp, yp, xp, op, rp, M, C, g.tx, g.rows_per_cta, mean, invstd, a, b1, b2);
+    else bn_bwd_apply_kernel<T, true, false><<<grid, kBNThreads, 0, st>>>(dp, yp, xp, op, rp, M, C, g.tx, g.rows_per_cta, mean, invstd, a, b1, b2);
+  } else {
+    if (dres) bn_bwd_apply_kernel<T, false, true><<<grid, kBNThreads, 0, st>>>(dp, yp, xp, op, rp, M, C, g.tx, g.rows_per_cta, mean, invstd, a, b1, b2);
+    else bn_bwd_apply_kernel<T, false, false><<<grid, kBNThreads, 0, st>>>(dp, yp, xp, op, rp, M, C, g.tx, g.rows_per_cta, mean, invstd, a, b1, b2);
+  }
+  return check_cuda(cudaGetLastError(), "bn_backward launch");
+}
+
+int bn_check(uint64_t M, int C, int dtype, const void* a, const void* b) {
+  if (dtype != FMPI_F32 && dtype != FMPI_BF16 && dtype != FMPI_F16) return set_error("batch norm: f32 / bf16 / f16 only");
+  const int N = dtype == FMPI_F32 ? 4 : 8;
+  if (M == 0 || C <= 0 || C % N) return set_error("batch norm: C = %d must be a positive multiple of %d", C, N);
+  if ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) & 15) return set_error("batch norm: 16-byte aligned tensors required");
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t fmpi_bn_scratch_bytes(int C) { return bn_scratch_floats(C) * sizeof(float); }
+
+int fmpi_bn_forward(const void* x, const void* res, void* y, uint64_t M, int C, int dtype, const float* gamma,
+                    const float* beta, float* running_mean, float* running_var, float momentum, float eps, int relu,
+                    float* save_mean, float* save_invstd, void* scratch, fmpi_stream st) {
+  if (bn_check(M, C, dtype, x, y)) return 1;
+  if (!save_mean || !save_invstd || !scratch) return set_error("batch norm: null output / scratch");
+  cudaStream_t s = static_cast<cudaStream_t>(st);
+  float* sc = static_cast<float*>(scratch);
+  switch (dtype) {
+    case FMPI_F32: return bn_forward_t<float>(x, res, y, M, C, gamma, beta, running_mean, running_var, momentum, eps, relu, save_mean, save_invstd, sc, s);
+    case FMPI_BF16: return bn_forward_t<__nv_bfloat16>(x, res, y, M, C, gamma, beta, running_mean, running_var, momentum, eps, relu, save_mean, save_invstd, sc, s);
+    default: return bn_forward_t<__half>(x, res, y, M, C, gamma, beta, running_mean, running_var, momentum, eps, relu, save_mean, save_invstd, sc, s);
+  }
+}
+
+int fmpi_bn_apply(const void* x, const void* res, void* y, uint64_t M, int C, int dtype, const float* scale,
+                  const float* shift, int relu, fmpi_stream st) {
+  if (bn_check(M, C, dtype, x, y)) return 1;
+  cudaStream_t s = static_cast<cudaStream_t>(st);
+  switch (dtype) {
+    case FMPI_F32: return bn_apply_t<float>(x, res, y, M, C, scale, shift, relu, s);
+    case FMPI_BF16: return bn_apply_t<__nv_bfloat16>(x, res, y, M, C, scale, shift, relu, s);
+    default: return bn_apply_t<__half>(x, res, y, M, C, scale, shift, relu, s);
+  }
+}
+
+int fmpi_bn_backward(const void* dy, const void* y, const void* x, void* dx, void* dres, uint64_t M, int C, int dtype,
+                     const float* gamma, const float* save_mean, const float* save_invstd, float* dgamma,
+                     float* dbeta, int relu, void* scratch, fmpi_stream st) {
+  if (bn_check(M, C, dtype, dy, dx)) return 1;
+  if (relu && !y) return set_error("batch norm backward: the fused ReLU needs the forward output");
+  if (!scratch) return set_error("batch norm: null scratch");
+  cudaStream_t s = static_cast<cudaStream_t>(st);
+  float* sc = static_cast<float*>(scratch);
+  switch (dtype) {
+    case FMPI_F32: return bn_backward_t<float>(dy, y, x, dx, dres, M, C, gamma, save_mean, save_invstd, dgamma, dbeta, relu, sc, s);
+    case FMPI_BF16: return bn_backward_t<__nv_bfloat16>(dy, y, x, dx, dres, M, C, gamma, save_mean, save_invstd, dgamma, dbeta, relu, sc, s);
+    default: return bn_backward_t<__half>(dy, y, x, dx, dres, M, C, gamma, save_mean, save_invstd, dgamma, dbeta, relu, sc, s);
+  }
+}
+
+}  // extern "C"

@@ -30,6 +30,7 @@ CUDA_SOURCES = [
     "kernels/fused_step.cu",
     "kernels/multi_tensor.cu",
     "kernels/reduce_diag.cu",
+    "kernels/batchnorm.cu",
 ]
 
 NVCC_ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]

@@ -194,6 +194,12 @@ def cuda():
         lib.fmpi_sumsq.argtypes = [vp, u64, i32, vp, vp, vp]
         lib.fmpi_checksum.argtypes = [vp, u64, vp, vp, vp]
         lib.fmpi_sumsq_noalloc.argtypes = [vp, u64, i32, vp, vp]
+        f32 = C.c_float
+        lib.fmpi_bn_scratch_bytes.argtypes = [i32]
+        lib.fmpi_bn_scratch_bytes.restype = C.c_size_t
+        lib.fmpi_bn_forward.argtypes = [vp, vp, vp, u64, i32, i32, vp, vp, vp, vp, f32, f32, i32, vp, vp, vp, vp]
+        lib.fmpi_bn_apply.argtypes = [vp, vp, vp, u64, i32, i32, vp, vp, i32, vp]
+        lib.fmpi_bn_backward.argtypes = [vp, vp, vp, vp, vp, u64, i32, i32, vp, vp, vp, vp, vp, i32, vp, vp]
         lib.fmpi_flush_l2.argtypes = [vp, u64, vp]
         _cuda = lib
     return _cuda

@@ -1,44 +1,61 @@
 """ResNet-50 (v1.5 bottleneck, 25,557,032 parameters) — the model of the headline benchmark
 (BASELINE.json: "ResNet-50 synthetic 224x224 ImageNet-shape data-parallel"). The reference
 ships no model code at all (model math lives in Lux/Flux); its README points to an
-external ImageNet example (/root/reference/README.md:78). Forward/backward are PyTorch/cuDNN;
-the framework's own kernels are on the gradient/optimiser/communication path."""
+external ImageNet example (/root/reference/README.md:78).
+
+``fused_bn=True`` replaces every BatchNorm2d (+ the ReLU and the residual add behind it) by
+:class:`fluxmpi_b200.ops.batchnorm.FusedBatchNormAct` — hand-written channels-last kernels —
+because on B200 those memory-bound ops, not the convolutions, are ~75 % of the step
+(profiles/README.md §7). Parameter names, shapes and state-dict keys are identical either way.
+Convolutions stay in PyTorch/cuDNN.
+"""
 from __future__ import annotations
 
 import torch
 from torch import nn
 
+from ..ops.batchnorm import FusedBatchNormAct
+
+
+def _bn(planes: int, relu: bool, fused: bool) -> nn.Module:
+    return FusedBatchNormAct(planes, relu=relu) if fused else nn.BatchNorm2d(planes)
+
 
 class Bottleneck(nn.Module):
     expansion = 4
 
-    def __init__(self, inplanes: int, planes: int, stride: int = 1, downsample: nn.Module | None = None):
+    def __init__(self, inplanes: int, planes: int, stride: int = 1, downsample: nn.Module | None = None,
+                 fused_bn: bool = False):
         super().__init__()
+        self.fused_bn = fused_bn
         self.conv1 = nn.Conv2d(inplanes, planes, 1, bias=False)
-        self.bn1 = nn.BatchNorm2d(planes)
+        self.bn1 = _bn(planes, True, fused_bn)
         self.conv2 = nn.Conv2d(planes, planes, 3, stride=stride, padding=1, bias=False)
-        self.bn2 = nn.BatchNorm2d(planes)
+        self.bn2 = _bn(planes, True, fused_bn)
         self.conv3 = nn.Conv2d(planes, planes * self.expansion, 1, bias=False)
-        self.bn3 = nn.BatchNorm2d(planes * self.expansion)
+        self.bn3 = _bn(planes * self.expansion, True, fused_bn)
         self.relu = nn.ReLU(inplace=True)
         self.downsample = downsample
 
     def forward(self, x):
-        identity = x
+        identity = x if self.downsample is None else self.downsample(x)
+        if self.fused_bn:
+            out = self.bn1(self.conv1(x))                       # bn + relu in one pass
+            out = self.bn2(self.conv2(out))
+            return self.bn3(self.conv3(out), identity)          # bn + add + relu in one pass
         out = self.relu(self.bn1(self.conv1(x)))
         out = self.relu(self.bn2(self.conv2(out)))
         out = self.bn3(self.conv3(out))
-        if self.downsample is not None:
-            identity = self.downsample(x)
         return self.relu(out + identity)
 
 
 class ResNet(nn.Module):
-    def __init__(self, layers=(3, 4, 6, 3), num_classes: int = 1000, width: int = 64):
+    def __init__(self, layers=(3, 4, 6, 3), num_classes: int = 1000, width: int = 64, fused_bn: bool = False):
         super().__init__()
+        self.fused_bn = fused_bn
         self.inplanes = width
         self.conv1 = nn.Conv2d(3, width, 7, stride=2, padding=3, bias=False)
-        self.bn1 = nn.BatchNorm2d(width)
+        self.bn1 = _bn(width, True, fused_bn)
         self.relu = nn.ReLU(inplace=True)
         self.maxpool = nn.MaxPool2d(3, stride=2, padding=1)
         self.layer1 = self._make_layer(width, layers[0])
@@ -59,22 +76,25 @@ class ResNet(nn.Module):
         if stride != 1 or self.inplanes != planes * Bottleneck.expansion:
             downsample = nn.Sequential(
                 nn.Conv2d(self.inplanes, planes * Bottleneck.expansion, 1, stride=stride, bias=False),
-                nn.BatchNorm2d(planes * Bottleneck.expansion))
-        layers = [Bottleneck(self.inplanes, planes, stride, downsample)]
+                _bn(planes * Bottleneck.expansion, False, self.fused_bn))
+        layers = [Bottleneck(self.inplanes, planes, stride, downsample, self.fused_bn)]
         self.inplanes = planes * Bottleneck.expansion
-        layers += [Bottleneck(self.inplanes, planes) for _ in range(1, blocks)]
+        layers += [Bottleneck(self.inplanes, planes, fused_bn=self.fused_bn) for _ in range(1, blocks)]
         return nn.Sequential(*layers)
 
     def forward(self, x):
-        x = self.maxpool(self.relu(self.bn1(self.conv1(x))))
+        x = self.bn1(self.conv1(x))
+        if not self.fused_bn:
+            x = self.relu(x)
+        x = self.maxpool(x)
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         return self.fc(torch.flatten(self.avgpool(x), 1))
 
 
-def resnet50(num_classes: int = 1000) -> ResNet:
-    return ResNet((3, 4, 6, 3), num_classes)
+def resnet50(num_classes: int = 1000, fused_bn: bool = False) -> ResNet:
+    return ResNet((3, 4, 6, 3), num_classes, fused_bn=fused_bn)
 
 
-def resnet_tiny(num_classes: int = 10) -> ResNet:
+def resnet_tiny(num_classes: int = 10, fused_bn: bool = False) -> ResNet:
     """Same topology, 1 block per stage, width 16 — for smoke tests."""
-    return ResNet((1, 1, 1, 1), num_classes, width=16)
+    return ResNet((1, 1, 1, 1), num_classes, width=16, fused_bn=fused_bn)

@@ -233,6 +233,29 @@ int fmpi_checksum(const void* x, uint64_t nbytes, uint64_t* out, void* scratch, 
 #define FMPI_NOALLOC_MAX_COUNT (1ull << 28)
 int fmpi_sumsq_noalloc(const void* x, uint64_t count, int dtype, double* out, fmpi_stream st);
 
+/* ---- channels-last batch normalisation fused with the residual add and ReLU that follow it
+ * (csrc/kernels/batchnorm.cu). x, res, y, dy, dx, dres are [M, C] row-major (NHWC memory) in
+ * `dtype` (f32 / bf16 / f16; C a multiple of 4 resp. 8, 16-byte aligned); gamma, beta, the
+ * running and saved statistics and the gradients of gamma / beta are fp32 [C]. `scratch` is a
+ * device buffer of fmpi_bn_scratch_bytes(C) that calls on one stream may share.
+ *   forward : y = relu?(batchnorm(x) (+ res)); updates running stats; saves mean / invstd
+ *   apply   : y = relu?(x * scale + shift (+ res))           (inference, precomputed affine)
+ *   backward: dx, dgamma, dbeta (and dres = dy masked by the ReLU when res was given); `y` is
+ *             the forward output (needed only when relu != 0).
+ * The reference ships no model code; this exists because these ops, not the
+ * convolutions, dominate the headline ResNet-50 step on B200 (profiles/README.md §7). */
+size_t fmpi_bn_scratch_bytes(int C);
+int fmpi_bn_forward(const void* x, const void* res, void* y, uint64_t M, int C, int dtype,
+                    const float* gamma, const float* beta, float* running_mean, float* running_var,
+                    float momentum, float eps, int relu, float* save_mean, float* save_invstd,
+                    void* scratch, fmpi_stream st);
+int fmpi_bn_apply(const void* x, const void* res, void* y, uint64_t M, int C, int dtype,
+                  const float* scale, const float* shift, int relu, fmpi_stream st);
+int fmpi_bn_backward(const void* dy, const void* y, const void* x, void* dx, void* dres, uint64_t M,
+                     int C, int dtype, const float* gamma, const float* save_mean,
+                     const float* save_invstd, float* dgamma, float* dbeta, int relu, void* scratch,
+                     fmpi_stream st);
+
 /* Write > L2-size bytes (bench hygiene: flush L2 between timed iterations). */
 int fmpi_flush_l2(void* buf, uint64_t nbytes, fmpi_stream st);
 

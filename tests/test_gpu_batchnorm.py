@@ -1,0 +1,136 @@
+"""Fused channels-last BatchNorm (+ residual add + ReLU) kernels against PyTorch's own ops
+evaluated in fp32 — forward output, running statistics, and every gradient."""
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+if not torch.cuda.is_available():
+    pytest.skip("needs a CUDA device", allow_module_level=True)
+
+from fluxmpi_b200 import _native
+from fluxmpi_b200.models import resnet_tiny
+from fluxmpi_b200.ops.batchnorm import FusedBatchNormAct, fused_bn_act, kernel_ok
+
+SHAPES = [(4, 64, 12, 12), (2, 8, 5, 7), (3, 256, 7, 7), (2, 2048, 3, 3), (5, 24, 9, 4), (2, 128, 56, 56)]
+
+
+def reference(x, res, w, b, rm, rv, relu, momentum=0.1, eps=1e-5):
+    """PyTorch ops in fp32 on the (possibly 16-bit) inputs."""
+    xf = x.float().detach().requires_grad_(True)
+    rf = res.float().detach().requires_grad_(True) if res is not None else None
+    wf, bf = w.detach().clone().requires_grad_(True), b.detach().clone().requires_grad_(True)
+    y = F.batch_norm(xf, rm, rv, wf, bf, True, momentum, eps)
+    if rf is not None:
+        y = y + rf
+    if relu:
+        y = F.relu(y)
+    return xf, rf, wf, bf, y
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("relu,use_res", [(False, False), (True, False), (True, True), (False, True)])
+def test_forward_backward_match_pytorch(shape, dtype, relu, use_res):
+    g = torch.Generator().manual_seed(hash((shape, relu, use_res)) % 1000)
+    N, C, H, W = shape
+    cl = lambda t: t.cuda().to(dtype).contiguous(memory_format=torch.channels_last)
+    x = cl(torch.randn(shape, generator=g) * 1.7 + 0.3)
+    res = cl(torch.randn(shape, generator=g)) if use_res else None
+    w = (torch.rand(C, generator=g) + 0.5).cuda()
+    b = (torch.randn(C, generator=g) * 0.2).cuda()
+    rm0, rv0 = torch.zeros(C).cuda(), torch.ones(C).cuda()
+    assert kernel_ok(x, res)
+
+    xr, rr, wr, br, yr = reference(x, res, w, b, rm0.clone(), rv0.clone(), relu)
+    rm_ref, rv_ref = rm0.clone(), rv0.clone()
+    F.batch_norm(x.float(), rm_ref, rv_ref, w, b, True, 0.1, 1e-5)
+
+    xk = x.clone().requires_grad_(True)
+    rk = res.clone().requires_grad_(True) if res is not None else None
+    wk, bk = w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    rm, rv = rm0.clone(), rv0.clone()
+    before = _native.launch_count
+    y = fused_bn_act(xk, wk, bk, rm, rv, True, 0.1, 1e-5, relu=relu, residual=rk)
+    assert _native.launch_count - before == 3, "the kernel path must be the one that runs"
+    assert y.dtype == dtype and y.is_contiguous(memory_format=torch.channels_last)
+
+    lo = dtype != torch.float32
+    tol = dict(rtol=2e-2, atol=3e-2) if lo else dict(rtol=1e-4, atol=1e-4)
+    assert torch.allclose(y.float(), yr, **tol), (y.float() - yr).abs().max()
+    assert torch.allclose(rm, rm_ref, rtol=1e-4, atol=1e-5) and torch.allclose(rv, rv_ref, rtol=1e-4, atol=1e-5)
+
+    dy = cl(torch.randn(shape, generator=g))
+    yr.backward(dy.float())
+    y.backward(dy)
+    gt = dict(rtol=3e-2, atol=3e-2) if lo else dict(rtol=2e-3, atol=2e-4)
+    # the ReLU mask comes from the rounded output; elements within rounding of zero may flip, so
+    # allow a handful of outliers in 16-bit and compare the rest tightly
+    def close(a, b, frac=0.0):
+        bad = ~torch.isclose(a.float(), b.float(), **gt)
+        return float(bad.float().mean()) <= frac, float((a.float() - b.float()).abs().max())
+    ok, worst = close(xk.grad, xr.grad, 2e-3 if lo else 0.0)
+    assert ok, worst
+    scale = max(1.0, float(wr.grad.abs().max()))
+    assert torch.allclose(wk.grad, wr.grad, rtol=3e-2 if lo else 1e-3, atol=(3e-2 if lo else 1e-3) * scale)
+    scale = max(1.0, float(br.grad.abs().max()))
+    assert torch.allclose(bk.grad, br.grad, rtol=3e-2 if lo else 1e-3, atol=(3e-2 if lo else 1e-3) * scale)
+    if use_res:
+        ok, worst = close(rk.grad, rr.grad, 2e-3 if lo else 0.0)
+        assert ok, worst
+
+
+def test_module_matches_batchnorm2d_train_and_eval():
+    torch.manual_seed(0)
+    ref = torch.nn.BatchNorm2d(32).cuda()
+    ours = FusedBatchNormAct(32, relu=True).cuda()
+    ours.load_state_dict(ref.state_dict())                  # same keys
+    x = torch.randn(6, 32, 10, 10, device="cuda").contiguous(memory_format=torch.channels_last)
+    for _ in range(3):
+        a = F.relu(ref(x))
+        b = ours(x)
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-4)
+    assert int(ours.num_batches_tracked) == 3
+    assert torch.allclose(ours.running_mean, ref.running_mean, rtol=1e-4, atol=1e-5)
+    assert torch.allclose(ours.running_var, ref.running_var, rtol=1e-4, atol=1e-5)
+    ref.eval(); ours.eval()
+    before = _native.launch_count
+    assert torch.allclose(F.relu(ref(x)), ours(x), rtol=1e-4, atol=1e-4)
+    assert _native.launch_count - before == 1               # inference: one elementwise kernel
+    # layouts / devices the kernels do not cover fall back to the stock ops
+    xn = torch.randn(6, 32, 10, 10, device="cuda")          # NCHW
+    assert not kernel_ok(xn)
+    assert torch.allclose(F.relu(ref(xn)), ours(xn), rtol=1e-4, atol=1e-4)
+    cpu = FusedBatchNormAct(6, relu=False)
+    assert cpu(torch.randn(2, 6, 3, 3)).shape == (2, 6, 3, 3)
+
+
+def test_resnet_fused_equals_unfused_training_steps():
+    """Whole-model check under the bench configuration (channels_last, bf16 autocast)."""
+    torch.manual_seed(3)
+    a = resnet_tiny(fused_bn=False).cuda().to(memory_format=torch.channels_last)
+    b = resnet_tiny(fused_bn=True).cuda().to(memory_format=torch.channels_last)
+    b.load_state_dict(a.state_dict())
+    oa = torch.optim.SGD(a.parameters(), lr=0.05)
+    ob = torch.optim.SGD(b.parameters(), lr=0.05)
+    g = torch.Generator().manual_seed(1)
+    for step in range(4):
+        x = torch.randn(16, 3, 64, 64, generator=g).cuda().contiguous(memory_format=torch.channels_last)
+        y = torch.randint(0, 10, (16,), generator=g).cuda()
+        losses = []
+        for m, o in ((a, oa), (b, ob)):
+            o.zero_grad()
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = F.cross_entropy(m(x), y)
+            loss.backward()
+            o.step()
+            losses.append(float(loss.detach()))
+        assert abs(losses[0] - losses[1]) < 0.05 * max(1.0, abs(losses[0])), (step, losses)
+    for (n, pa), (_, pb) in zip(a.named_parameters(), b.named_parameters()):
+        d = (pa - pb).abs()
+        assert float(d.mean()) < 5e-3, (n, float(d.mean()))
+    for (n, ba), (_, bb) in zip(a.named_buffers(), b.named_buffers()):
+        assert torch.allclose(ba.float(), bb.float(), rtol=5e-2, atol=5e-2), n
