@@ -39,7 +39,7 @@ __host__ inline BNGeom bn_geom(uint64_t M, int VC) {
   while (g.tx < 32 && g.tx * 2 <= VC) g.tx *= 2;
   g.ty = kBNThreads / g.tx;
   g.gy = (VC + g.tx - 1) / g.tx;
-  uint64_t want = (148ull * 8 + g.gy - 1) / g.gy;
+  uint64_t want = (148ull * 3 + g.gy - 1) / g.gy;   // ~3 CTAs per SM; fewer partials to fold
   const uint64_t max_gx = (M + g.ty - 1) / g.ty;
   if (want > max_gx) want = max_gx;
   if (want > kBNMaxGx) want = kBNMaxGx;
@@ -138,17 +138,44 @@ bn_stats_kernel(const T* __restrict__ x, uint64_t M, int C, int tx, uint64_t row
   }
 }
 
-__global__ void bn_fwd_finalize_kernel(const float* __restrict__ partial, unsigned gx, uint64_t M, int C,
-                                       const float* __restrict__ gamma, const float* __restrict__ beta,
-                                       float* running_mean, float* running_var, float momentum, float eps,
-                                       float* save_mean, float* save_invstd, float* scale, float* shift) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double s = 0.0, q = 0.0;
-  for (unsigned g = 0; g < gx; ++g) {
-    s += double(partial[uint64_t(g) * 2 * C + c]);
-    q += double(partial[uint64_t(g) * 2 * C + C + c]);
+// Fold the per-CTA partials of 32 channels with a 32 x 32 thread block: lane x = channel,
+// lane y strides over the row chunks; doubles in shared memory, tree over y. (A one-thread-
+// per-channel loop over ~10^3 partials took > 100 us per layer and was the top kernel of the
+// step.) Returns the two sums in (s, q), valid where threadIdx.y == 0.
+constexpr int kFoldC = 32, kFoldG = 32;
+__device__ __forceinline__ void fold_partials(const float* __restrict__ partial, unsigned gx, int C, int c,
+                                              double& s, double& q) {
+  __shared__ double sh[2][kFoldG][kFoldC + 1];
+  s = 0.0;
+  q = 0.0;
+  if (c < C)
+    for (unsigned g = threadIdx.y; g < gx; g += kFoldG) {
+      s += double(partial[uint64_t(g) * 2 * C + c]);
+      q += double(partial[uint64_t(g) * 2 * C + C + c]);
+    }
+  sh[0][threadIdx.y][threadIdx.x] = s;
+  sh[1][threadIdx.y][threadIdx.x] = q;
+  __syncthreads();
+  for (int off = kFoldG / 2; off > 0; off >>= 1) {
+    if (int(threadIdx.y) < off) {
+      sh[0][threadIdx.y][threadIdx.x] += sh[0][threadIdx.y + off][threadIdx.x];
+      sh[1][threadIdx.y][threadIdx.x] += sh[1][threadIdx.y + off][threadIdx.x];
+    }
+    __syncthreads();
   }
+  s = sh[0][0][threadIdx.x];
+  q = sh[1][0][threadIdx.x];
+}
+
+__global__ void __launch_bounds__(kFoldC * kFoldG)
+bn_fwd_finalize_kernel(const float* __restrict__ partial, unsigned gx, uint64_t M, int C,
+                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                       float* running_mean, float* running_var, float momentum, float eps,
+                       float* save_mean, float* save_invstd, float* scale, float* shift) {
+  const int c = blockIdx.x * kFoldC + threadIdx.x;
+  double s, q;
+  fold_partials(partial, gx, C, c, s, q);
+  if (c >= C || threadIdx.y != 0) return;
   const double mean = s / double(M);
   double var = q / double(M) - mean * mean;
   if (var < 0.0) var = 0.0;
@@ -268,16 +295,14 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T*
   }
 }
 
-__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, unsigned gx, uint64_t M, int C,
-                                       const float* __restrict__ gamma, const float* __restrict__ invstd,
-                                       float* dgamma, float* dbeta, float* a, float* b1, float* b2) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double s1 = 0.0, s2 = 0.0;
-  for (unsigned g = 0; g < gx; ++g) {
-    s1 += double(partial[uint64_t(g) * 2 * C + c]);
-    s2 += double(partial[uint64_t(g) * 2 * C + C + c]);
-  }
+__global__ void __launch_bounds__(kFoldC * kFoldG)
+bn_bwd_finalize_kernel(const float* __restrict__ partial, unsigned gx, uint64_t M, int C,
+                       const float* __restrict__ gamma, const float* __restrict__ invstd,
+                       float* dgamma, float* dbeta, float* a, float* b1, float* b2) {
+  const int c = blockIdx.x * kFoldC + threadIdx.x;
+  double s1, s2;
+  fold_partials(partial, gx, C, c, s1, s2);
+  if (c >= C || threadIdx.y != 0) return;
   if (dbeta) dbeta[c] = float(s1);
   if (dgamma) dgamma[c] = float(s2);
   a[c] = (gamma ? gamma[c] : 1.f) * invstd[c];
@@ -363,7 +388,7 @@ int bn_forward_t(const void* x, const void* res, void* y, uint64_t M, int C, con
   const dim3 grid(g.gx, g.gy);
   const size_t smem = size_t(kBNThreads) * 2 * N * sizeof(float);
   bn_stats_kernel<T><<<grid, kBNThreads, smem, st>>>(static_cast<const T*>(x), M, C, g.tx, g.rows_per_cta, partial);
-  bn_fwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, g.gx, M, C, gamma, beta, rmean, rvar, momentum,
+  bn_fwd_finalize_kernel<<<(C + kFoldC - 1) / kFoldC, dim3(kFoldC, kFoldG), 0, st>>>(partial, g.gx, M, C, gamma, beta, rmean, rvar, momentum,
                                                           eps, save_mean, save_invstd, scale, shift);
   const T* xp = static_cast<const T*>(x);
   const T* rp = static_cast<const T*>(res);
@@ -416,7 +441,7 @@ int bn_backward_t(const void* dy, const void* y, const void* x, void* dx, void* 
   T* rp = static_cast<T*>(dres);
   if (relu) bn_bwd_reduce_kernel<T, true><<<grid, kBNThreads, smem, st>>>(dp, yp, xp, M, C, g.tx, g.rows_per_cta, mean, invstd, partial);
   else bn_bwd_reduce_kernel<T, false><<<grid, kBNThreads, smem, st>>>(dp, yp, xp, M, C, g.tx, g.rows_per_cta, mean, invstd, partial);
-  bn_bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partial, g.gx, M, C, gamma, invstd, dgamma, dbeta, a, b1, b2);
+  bn_bwd_finalize_kernel<<<(C + kFoldC - 1) / kFoldC, dim3(kFoldC, kFoldG), 0, st>>>(partial, g.gx, M, C, gamma, invstd, dgamma, dbeta, a, b1, b2);
   if (relu) {
     if (dres) bn_bwd_apply_kernel<T, true, true><<<grid, kBNThreads, 0, st>>>(dp, yp, xp, op, rp, M, C, g.tx, g.rows_per_cta, mean, invstd, a, b1, b2);
     else bn_bwd_apply_kernel<T, true, false><<<grid, kBNThreads, 0, st>>>(dp, yp, xp, op, rp, M, C, g.tx, g.rows_per_cta, mean, invstd, a, b1, b2);
