@@ -31,6 +31,7 @@ CUDA_SOURCES = [
     "kernels/multi_tensor.cu",
     "kernels/reduce_diag.cu",
     "kernels/batchnorm.cu",
+    "kernels/pool.cu",
 ]
 
 NVCC_ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]

@@ -15,6 +15,7 @@ import torch
 from torch import nn
 
 from ..ops.batchnorm import FusedBatchNormAct
+from ..ops.pool import FusedMaxPool2d
 
 
 def _bn(planes: int, relu: bool, fused: bool) -> nn.Module:
@@ -57,7 +58,7 @@ class ResNet(nn.Module):
         self.conv1 = nn.Conv2d(3, width, 7, stride=2, padding=3, bias=False)
         self.bn1 = _bn(width, True, fused_bn)
         self.relu = nn.ReLU(inplace=True)
-        self.maxpool = nn.MaxPool2d(3, stride=2, padding=1)
+        self.maxpool = FusedMaxPool2d(3, 2, 1) if fused_bn else nn.MaxPool2d(3, stride=2, padding=1)
         self.layer1 = self._make_layer(width, layers[0])
         self.layer2 = self._make_layer(width * 2, layers[1], stride=2)
         self.layer3 = self._make_layer(width * 4, layers[2], stride=2)

@@ -256,6 +256,14 @@ int fmpi_bn_backward(const void* dy, const void* y, const void* x, void* dx, voi
                      const float* save_invstd, float* dgamma, float* dbeta, int relu, void* scratch,
                      fmpi_stream st);
 
+/* ---- channels-last max pooling (csrc/kernels/pool.cu): x [N,H,W,C] -> y [N,OH,OW,C] with
+ * OH = (H + 2P - K)/S + 1; idx keeps one byte per output element (window position of the
+ * maximum) for the atomics-free gather backward. */
+int fmpi_maxpool_fwd(const void* x, void* y, uint8_t* idx, int N, int H, int W, int C, int K, int S,
+                     int P, int dtype, fmpi_stream st);
+int fmpi_maxpool_bwd(const void* dy, const uint8_t* idx, void* dx, int N, int H, int W, int C, int K,
+                     int S, int P, int dtype, fmpi_stream st);
+
 /* Write > L2-size bytes (bench hygiene: flush L2 between timed iterations). */
 int fmpi_flush_l2(void* buf, uint64_t nbytes, fmpi_stream st);
 

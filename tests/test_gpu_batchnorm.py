@@ -108,6 +108,37 @@ def test_module_matches_batchnorm2d_train_and_eval():
     assert cpu(torch.randn(2, 6, 3, 3)).shape == (2, 6, 3, 3)
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("shape,k,s,p", [((4, 64, 32, 32), 3, 2, 1), ((2, 8, 7, 9), 3, 2, 1), ((3, 16, 10, 10), 2, 2, 0),
+                                         ((2, 24, 11, 6), 3, 1, 1), ((1, 8, 5, 5), 5, 3, 2)])
+def test_maxpool_nhwc_matches_pytorch(dtype, shape, k, s, p):
+    from fluxmpi_b200.ops.pool import FusedMaxPool2d, kernel_ok as pool_ok
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(shape, generator=g).cuda().to(dtype).contiguous(memory_format=torch.channels_last)
+    assert pool_ok(x)
+    xa = x.clone().requires_grad_(True)
+    xb = x.clone().requires_grad_(True)
+    before = _native.launch_count
+    ya = FusedMaxPool2d(k, s, p)(xa)
+    assert _native.launch_count - before == 1
+    yb = F.max_pool2d(xb, k, s, p)
+    assert ya.shape == yb.shape and torch.equal(ya, yb)
+    assert ya.is_contiguous(memory_format=torch.channels_last)
+    dy = torch.randn(yb.shape, generator=g).cuda().to(dtype).contiguous(memory_format=torch.channels_last)
+    ya.backward(dy)
+    yb.backward(dy)
+    # overlapping windows add several gradients into one input: fp32 accumulation here, so allow
+    # a rounding step in 16-bit
+    tol = dict(rtol=1e-2, atol=1e-2) if dtype != torch.float32 else dict(rtol=1e-6, atol=1e-6)
+    assert torch.allclose(xa.grad.float(), xb.grad.float(), **tol)
+    # ties: the first maximum in scan order takes the gradient, like PyTorch
+    t = torch.ones(1, 8, 4, 4, device="cuda", dtype=dtype).contiguous(memory_format=torch.channels_last)
+    ta, tb = t.clone().requires_grad_(True), t.clone().requires_grad_(True)
+    FusedMaxPool2d(2, 2, 0)(ta).sum().backward()
+    F.max_pool2d(tb, 2, 2, 0).sum().backward()
+    assert torch.equal(ta.grad, tb.grad)
+
+
 def test_resnet_fused_equals_unfused_training_steps():
     """Whole-model check under the bench configuration (channels_last, bf16 autocast)."""
     torch.manual_seed(3)
