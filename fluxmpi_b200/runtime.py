@@ -112,8 +112,13 @@ def _job_name() -> str:
     if job:
         return job
     port = os.environ.get("MASTER_PORT", "0")
-    run = os.environ.get("TORCHELASTIC_RUN_ID", "none")
-    return f"{port}-{run}-{os.getuid()}"
+    run = os.environ.get("TORCHELASTIC_RUN_ID")
+    if run is not None:
+        # under torchrun every worker is a child of the same agent process: its pid makes the
+        # name unique per launch even when the port and the (default "none") run id repeat, so
+        # a segment left behind by a crashed earlier job can never be mistaken for this one
+        return f"{port}-{run}-{os.getuid()}-{os.getppid()}"
+    return f"{port}-none-{os.getuid()}"
 
 
 def Init(gpu_devices: Optional[Sequence[int]] = None, verbose: bool = False,
