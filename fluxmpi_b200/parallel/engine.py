@@ -418,6 +418,11 @@ class GraphedStep:
         self.static_in = tuple(torch.empty_like(x) for x in example_inputs)
         for s, x in zip(self.static_in, example_inputs):
             s.copy_(x)
+        # warm-up and capture run on side streams on purpose; autograd's "AccumulateGrad stream
+        # mismatch" notice is about exactly that and is not actionable here
+        quiet = getattr(torch.autograd.graph, "set_warn_on_accumulate_grad_stream_mismatch", None)
+        if quiet is not None:
+            quiet(False)
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
