@@ -13,7 +13,6 @@ from __future__ import annotations
 
 import argparse
 import json
-import os
 import sys
 from pathlib import Path
 
@@ -21,7 +20,6 @@ import torch
 
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import fluxmpi_b200 as fm                                    # noqa: E402
-from fluxmpi_b200 import _native                             # noqa: E402
 
 
 def time_op(fn, bufs, iters, warm, graph=False):

@@ -18,7 +18,6 @@ ignored (there is one world, like the reference's hard-coded ``MPI.COMM_WORLD``)
 """
 from __future__ import annotations
 
-import ctypes as C
 from concurrent.futures import Future
 from typing import Optional
 

@@ -14,7 +14,7 @@ copy of batch k+1 overlaps the compute of batch k.
 from __future__ import annotations
 
 import math
-from typing import Iterable, Iterator, Sequence
+from typing import Iterator, Sequence
 
 import torch
 

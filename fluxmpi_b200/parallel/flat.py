@@ -10,7 +10,7 @@ high-performance engine uses internally (one symmetric buffer, parameters are vi
 from __future__ import annotations
 
 from collections import OrderedDict
-from typing import Any, Iterator, Mapping
+from typing import Iterator
 
 import torch
 

@@ -18,7 +18,6 @@ from __future__ import annotations
 
 import threading
 from dataclasses import dataclass
-from typing import Any
 
 import numpy as np
 import torch

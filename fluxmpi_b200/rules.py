@@ -16,9 +16,8 @@ Adam keeps ``(mt, vt, (β1^t, β2^t))`` exactly like Optimisers (ϵ outside the 
 """
 from __future__ import annotations
 
-import math
-from dataclasses import dataclass, field, replace
-from typing import Any, Sequence
+from dataclasses import dataclass, replace
+from typing import Any
 
 import torch
 

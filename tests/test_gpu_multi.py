@@ -11,7 +11,9 @@ if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
 from conftest import run_spmd
 
 NGPU = torch.cuda.device_count()
-WORLDS = sorted({2, min(4, NGPU), NGPU} & set(range(2, NGPU + 1)))
+# the smallest and the largest world the box allows (2 and 8 on a full node; 3 is covered in
+# single-GPU emulation and on the CPU backend) — keeps the tier's wall time bounded
+WORLDS = sorted({2, NGPU} & set(range(2, NGPU + 1)))
 
 
 def _run(script, w, **kw):
