@@ -242,3 +242,36 @@ def test_shipped_tuned_table_is_well_formed():
         for op in ("allreduce_any", "reduce_any", "bcast_any", "allreduce_symm", "bcast_symm"):
             rows = data[world][op]
             assert rows and all(r["algo"] in ("oneshot", "twoshot", "nvls") and 1 <= r["blocks"] <= 160 for r in rows)
+
+
+# ------------------------------------------------------------------------------ model ops (CPU fallbacks)
+def test_fused_ops_fall_back_to_stock_ops_off_gpu():
+    from fluxmpi_b200.models import resnet_tiny
+    from fluxmpi_b200.ops.batchnorm import FusedBatchNormAct
+    from fluxmpi_b200.ops.pool import FusedMaxPool2d
+    torch.manual_seed(0)
+    ref, ours = torch.nn.BatchNorm2d(6), FusedBatchNormAct(6, relu=True)
+    ours.load_state_dict(ref.state_dict())                        # identical keys
+    x, r = torch.randn(4, 6, 5, 5), torch.randn(4, 6, 5, 5)
+    assert torch.allclose(ours(x, r), torch.relu(ref(x) + r), atol=1e-6)
+    assert torch.allclose(ours.running_var, ref.running_var) and int(ours.num_batches_tracked) == 1
+    ours.eval(); ref.eval()
+    assert torch.allclose(ours(x), torch.relu(ref(x)), atol=1e-6)
+    assert torch.equal(FusedMaxPool2d(3, 2, 1)(x), torch.nn.functional.max_pool2d(x, 3, 2, 1))
+    a, b = resnet_tiny(fused_bn=True), resnet_tiny(fused_bn=False)
+    b.load_state_dict(a.state_dict())
+    img = torch.randn(2, 3, 32, 32)
+    assert torch.allclose(a(img), b(img), atol=1e-5)
+    assert sum(p.numel() for p in a.parameters()) == sum(p.numel() for p in b.parameters())
+
+
+def test_device_loader_cpu_shuffle_and_remainder():
+    xs, ys = torch.arange(23.0).reshape(23, 1), torch.arange(23)
+    data = fm.DistributedDataContainer(fm.TensorDataset(xs, ys), rank=0, world=1)
+    loader = fm.DeviceLoader(data, 5, device="cpu", shuffle=True, drop_last=False, seed=3)
+    seen = [int(v) for _, yb in loader for v in yb]
+    assert sorted(seen) == list(range(23)) and seen != list(range(23))
+    assert len(loader) == 5
+    again = [int(v) for _, yb in loader for v in yb]
+    assert sorted(again) == list(range(23)) and again != seen      # a new permutation every epoch
+    assert len(fm.DeviceLoader(data, 5, device="cpu", drop_last=True)) == 4
