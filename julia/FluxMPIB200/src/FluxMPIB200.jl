@@ -32,6 +32,9 @@ include("runtime.jl")    # Init / ranks / printing
 include("sync_tree.jl")
 include("dist_optimizer.jl")
 include("sharding.jl")
+include("engine.jl")     # FlatEngine: fused all-reduce + optimiser step on a flat vector
+
+export FlatEngine, step!, params, grads
 
 """
     FluxMPIFluxModel(model)
