@@ -26,9 +26,17 @@
     }                                                                                \
   } while (0)
 
-static int run_rank(const char* name, int rank, int world) {
+static int run_rank(const char* name, int rank, int world, int nodes, int port) {
   fmpi_host_comm* c = NULL;
-  CHECK(fmpi_host_init(name, rank, world, 1 << 16, 30.0, &c));
+  if (nodes == 1) {
+    CHECK(fmpi_host_init(name, rank, world, 1 << 16, 30.0, &c));
+  } else { /* node-major ranks: shared memory per node, TCP mesh between the node leaders */
+    const int per = world / nodes;
+    char node_name[96];
+    snprintf(node_name, sizeof(node_name), "%s_n%d", name, rank / per);
+    CHECK(fmpi_host_init_multi(node_name, rank % per, per, rank / per, nodes, "127.0.0.1", port,
+                               1 << 16, 30.0, &c));
+  }
   if (fmpi_host_rank(c) != rank || fmpi_host_world(c) != world) return 2;
 
   /* allreduce, in place, a message larger than one staging slot (chunking) */
@@ -72,13 +80,15 @@ static int run_rank(const char* name, int rank, int world) {
 
 int main(int argc, char** argv) {
   const int world = argc > 1 ? atoi(argv[1]) : 3;
+  const int nodes = argc > 2 ? atoi(argv[2]) : 1; /* > 1: pretend nodes on this machine */
+  const int port = argc > 3 ? atoi(argv[3]) : 0;
   char name[64];
   snprintf(name, sizeof(name), "/fmpi_abitest_%d", (int)getpid());
   pid_t kids[FMPI_MAX_RANKS];
-  if (world < 1 || world > FMPI_MAX_RANKS) return 2;
+  if (world < 1 || world > FMPI_MAX_RANKS || nodes < 1 || world % nodes) return 2;
   for (int r = 0; r < world; ++r) {
     kids[r] = fork();
-    if (kids[r] == 0) _exit(run_rank(name, r, world));
+    if (kids[r] == 0) _exit(run_rank(name, r, world, nodes, port));
   }
   int bad = 0;
   for (int r = 0; r < world; ++r) {

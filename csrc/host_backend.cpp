@@ -22,6 +22,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 
@@ -211,8 +212,32 @@ void reduce_dispatch(int dt, const uint8_t* slots, size_t stride, int world, uin
 
 }  // namespace
 
+namespace fmpi_host_detail {
+int fail(const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return 1;
+}
+double now_s() { return ::now_s(); }
+size_t dtype_size(int dtype) { return ::dtype_size(dtype); }
+void reduce_slots(int dtype, const uint8_t* slots, size_t stride, int world, uint8_t* out,
+                  size_t lo, size_t hi, int op) {
+  reduce_dispatch(dtype, slots, stride, world, out, lo, hi, op);
+}
+}  // namespace fmpi_host_detail
+
+// `rank` / `world` are the shared-memory participants, i.e. the ranks of THIS node. With a
+// leader mesh attached (`net`) the job has nnodes * world ranks and global rank
+// node * world + rank; without one the two notions coincide.
 struct fmpi_host_comm {
   int rank = 0, world = 1;
+  int node = 0, nnodes = 1;
+  fmpi_net* net = nullptr;
+  bool heap = false;          // base came from aligned_alloc (one rank per node: no shm needed)
   size_t slot_bytes = 0;
   double timeout_s = 300.0;
   std::string name;
@@ -247,6 +272,17 @@ struct fmpi_host_comm {
     }
     local_gen = gen + 1;
     return 0;
+  }
+
+  // Every rank of the node calls this after the leader ran its inter-node step (rc = what that
+  // step returned; 0 on the other ranks). A failed leader poisons the node so the ranks waiting
+  // for it give up too; otherwise the node meets and may read what the leader brought back.
+  int leader_phase(int rc) {
+    if (rc) {
+      if (hdr) hdr->aborted.store(1, std::memory_order_relaxed);
+      return 1;
+    }
+    return barrier();
   }
 };
 
@@ -346,7 +382,10 @@ int fmpi_host_init(const char* name, int rank, int world, size_t slot_bytes, dou
 
 int fmpi_host_finalize(fmpi_host_comm* c) {
   if (!c) return 0;
-  if (c->base) {
+  if (c->net) fmpi_net_finalize(c->net);
+  if (c->heap) {
+    free(c->base);
+  } else if (c->base) {
     c->hdr->detached.fetch_add(1);
     munmap(c->base, c->map_bytes);
   }
@@ -354,12 +393,54 @@ int fmpi_host_finalize(fmpi_host_comm* c) {
   return 0;
 }
 
-int fmpi_host_rank(const fmpi_host_comm* c) { return c ? c->rank : -1; }
-int fmpi_host_world(const fmpi_host_comm* c) { return c ? c->world : -1; }
+int fmpi_host_init_multi(const char* name, int local_rank, int local_world, int node, int nnodes,
+                         const char* master_addr, int port, size_t slot_bytes, double timeout_s,
+                         fmpi_host_comm** out) {
+  if (!out || nnodes < 1 || node < 0 || node >= nnodes || local_world < 1 || local_rank < 0 ||
+      local_rank >= local_world)
+    return fail("fmpi_host_init_multi: bad arguments (node %d/%d, local rank %d/%d)", node, nnodes,
+                local_rank, local_world);
+  fmpi_host_comm* c = nullptr;
+  if (local_world > 1) {
+    if (fmpi_host_init(name, local_rank, local_world, slot_bytes, timeout_s, &c)) return 1;
+  } else {
+    // a node with a single rank needs no segment: one staging slot + the result slot on the heap
+    slot_bytes = (slot_bytes + 63) & ~size_t(63);
+    if (slot_bytes == 0) slot_bytes = size_t(4) << 20;
+    c = new fmpi_host_comm;
+    c->slot_bytes = slot_bytes;
+    c->timeout_s = timeout_s > 0 ? timeout_s : 300.0;
+    c->name = name ? name : "";
+    c->heap = true;
+    c->base = static_cast<uint8_t*>(aligned_alloc(4096, 2 * slot_bytes));
+    if (!c->base) { delete c; return fail("out of memory for %zu-byte staging", 2 * slot_bytes); }
+    c->slots = c->base;
+    c->result = c->base + slot_bytes;
+  }
+  c->node = node;
+  c->nnodes = nnodes;
+  if (nnodes > 1 && local_rank == 0) {
+    if (fmpi_net_init(master_addr, port, node, nnodes, c->timeout_s, &c->net)) {
+      if (c->hdr) c->hdr->aborted.store(1, std::memory_order_relaxed);
+      fmpi_host_finalize(c);
+      return 1;
+    }
+  }
+  // nobody leaves before its leader is connected, so the first collective cannot race the mesh
+  if (c->barrier()) { fmpi_host_finalize(c); return 1; }
+  *out = c;
+  return 0;
+}
+
+int fmpi_host_rank(const fmpi_host_comm* c) { return c ? c->node * c->world + c->rank : -1; }
+int fmpi_host_world(const fmpi_host_comm* c) { return c ? c->nnodes * c->world : -1; }
 
 int fmpi_host_barrier(fmpi_host_comm* c) {
   if (!c) return fail("null communicator");
-  return c->barrier();
+  if (c->barrier()) return 1;
+  if (c->nnodes == 1) return 0;
+  if (c->leader_phase(c->net ? fmpi_net_barrier(c->net) : 0)) return 1;
+  return 0;
 }
 
 int fmpi_host_allreduce(fmpi_host_comm* c, const void* send, void* recv, size_t count, int dtype,
@@ -368,7 +449,7 @@ int fmpi_host_allreduce(fmpi_host_comm* c, const void* send, void* recv, size_t 
   const size_t es = dtype_size(dtype);
   if (es == 0) return fail("unsupported dtype %d", dtype);
   if (op < FMPI_SUM || op > FMPI_MAX) return fail("unsupported op %d", op);
-  if (c->world == 1) {
+  if (c->world == 1 && c->nnodes == 1) {
     if (recv != send) memmove(recv, send, count * es);
     return 0;
   }
@@ -384,6 +465,10 @@ int fmpi_host_allreduce(fmpi_host_comm* c, const void* send, void* recv, size_t 
     const size_t hi = lo + per < n ? lo + per : n;
     if (hi > lo) reduce_dispatch(dtype, c->slots, c->slot_bytes, c->world, c->result, lo, hi, op);
     if (c->barrier()) return 1;
+    // the node's sum now sits in the result slot; the leader folds in the other nodes'
+    if (c->nnodes > 1 &&
+        c->leader_phase(c->net ? fmpi_net_allreduce(c->net, c->result, n, dtype, op) : 0))
+      return 1;
     memcpy(d + done * es, c->result, n * es);
   }
   // The result slot must stay intact until everyone has copied it out.
@@ -396,11 +481,13 @@ int fmpi_host_reduce(fmpi_host_comm* c, const void* send, void* recv, size_t cou
   const size_t es = dtype_size(dtype);
   if (es == 0) return fail("unsupported dtype %d", dtype);
   if (op < FMPI_SUM || op > FMPI_MAX) return fail("unsupported op %d", op);
-  if (root < 0 || root >= c->world) return fail("bad root %d", root);
-  if (c->world == 1) {
+  if (root < 0 || root >= c->nnodes * c->world) return fail("bad root %d", root);
+  if (c->world == 1 && c->nnodes == 1) {
     if (recv != send) memmove(recv, send, count * es);
     return 0;
   }
+  const int root_node = root / c->world;
+  const bool is_root = c->node == root_node && c->rank == root % c->world;
   const size_t chunk = c->slot_bytes / es;
   const uint8_t* s = static_cast<const uint8_t*>(send);
   uint8_t* d = static_cast<uint8_t*>(recv);
@@ -413,21 +500,29 @@ int fmpi_host_reduce(fmpi_host_comm* c, const void* send, void* recv, size_t cou
     const size_t hi = lo + per < n ? lo + per : n;
     if (hi > lo) reduce_dispatch(dtype, c->slots, c->slot_bytes, c->world, c->result, lo, hi, op);
     if (c->barrier()) return 1;
-    if (c->rank == root) memcpy(d + done * es, c->result, n * es);
+    if (c->nnodes > 1 &&
+        c->leader_phase(c->net ? fmpi_net_reduce(c->net, c->result, n, dtype, op, root_node) : 0))
+      return 1;
+    if (is_root) memcpy(d + done * es, c->result, n * es);
   }
   return c->barrier();
 }
 
 int fmpi_host_bcast(fmpi_host_comm* c, void* buf, size_t nbytes, int root) {
   if (!c) return fail("null communicator");
-  if (root < 0 || root >= c->world) return fail("bad root %d", root);
-  if (c->world == 1) return 0;
+  if (root < 0 || root >= c->nnodes * c->world) return fail("bad root %d", root);
+  if (c->world == 1 && c->nnodes == 1) return 0;
+  const int root_node = root / c->world;
+  const bool is_root = c->node == root_node && c->rank == root % c->world;
   uint8_t* b = static_cast<uint8_t*>(buf);
   for (size_t done = 0; done < nbytes; done += c->slot_bytes) {
     const size_t n = nbytes - done < c->slot_bytes ? nbytes - done : c->slot_bytes;
-    if (c->rank == root) memcpy(c->result, b + done, n);
+    if (is_root) memcpy(c->result, b + done, n);
     if (c->barrier()) return 1;
-    if (c->rank != root) memcpy(b + done, c->result, n);
+    if (c->nnodes > 1 &&
+        c->leader_phase(c->net ? fmpi_net_bcast(c->net, c->result, n, root_node) : 0))
+      return 1;
+    if (!is_root) memcpy(b + done, c->result, n);
     if (c->barrier()) return 1;
   }
   return 0;
@@ -437,13 +532,30 @@ int fmpi_host_allgather(fmpi_host_comm* c, const void* send, void* recv, size_t 
   if (!c) return fail("null communicator");
   if (nbytes_each > c->slot_bytes)
     return fail("allgather blob of %zu bytes exceeds the %zu-byte slot", nbytes_each, c->slot_bytes);
-  if (c->world == 1) {
+  if (c->world == 1 && c->nnodes == 1) {
     if (recv != send) memmove(recv, send, nbytes_each);
     return 0;
   }
+  uint8_t* d = static_cast<uint8_t*>(recv);
+  if (c->nnodes > 1) {
+    // node-major result: the leader packs its node's blobs, swaps packs with the other leaders
+    // and leaves the whole table in the result slot
+    const size_t node_bytes = size_t(c->world) * nbytes_each;
+    const size_t all = size_t(c->nnodes) * node_bytes;
+    if (all > c->slot_bytes)
+      return fail("allgather of %zu bytes in total exceeds the %zu-byte slot", all, c->slot_bytes);
+    memcpy(c->result + size_t(c->node) * node_bytes + size_t(c->rank) * nbytes_each, send,
+           nbytes_each);
+    if (c->barrier()) return 1;
+    if (c->leader_phase(c->net ? fmpi_net_allgather(c->net, c->result + size_t(c->node) * node_bytes,
+                                                    c->result, node_bytes)
+                               : 0))
+      return 1;
+    memcpy(d, c->result, all);
+    return c->barrier();
+  }
   memcpy(c->slots + size_t(c->rank) * c->slot_bytes, send, nbytes_each);
   if (c->barrier()) return 1;
-  uint8_t* d = static_cast<uint8_t*>(recv);
   for (int r = 0; r < c->world; ++r)
     memcpy(d + size_t(r) * nbytes_each, c->slots + size_t(r) * c->slot_bytes, nbytes_each);
   return c->barrier();

@@ -22,7 +22,7 @@ CSRC = ROOT / "csrc"
 INC = ROOT / "include"
 LIB = Path(__file__).resolve().parent / "_lib"
 
-HOST_SOURCES = ["host_backend.cpp", "fdx.cpp"]
+HOST_SOURCES = ["host_backend.cpp", "fdx.cpp", "net_backend.cpp"]
 CUDA_SOURCES = [
     "symm.cpp",
     "topo.cpp",

@@ -82,6 +82,18 @@ def host():
         lib.fmpi_fdx_bcast.argtypes = [C.c_int, C.c_char_p, C.c_int, C.c_int, C.c_int,
                                        C.POINTER(C.c_int), C.c_double]
         lib.fmpi_fdx_close.argtypes = [C.c_int, C.c_char_p, C.c_int]
+        lib.fmpi_host_init_multi.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                             C.c_char_p, C.c_int, C.c_size_t, C.c_double,
+                                             C.POINTER(C.c_void_p)]
+        lib.fmpi_net_init.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_double,
+                                      C.POINTER(C.c_void_p)]
+        lib.fmpi_net_finalize.argtypes = [C.c_void_p]
+        lib.fmpi_net_barrier.argtypes = [C.c_void_p]
+        lib.fmpi_net_allreduce.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int]
+        lib.fmpi_net_reduce.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int,
+                                        C.c_int]
+        lib.fmpi_net_bcast.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]
+        lib.fmpi_net_allgather.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
         _host = lib
     return _host
 

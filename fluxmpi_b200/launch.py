@@ -13,6 +13,7 @@ from __future__ import annotations
 
 import argparse
 import os
+import shutil
 import signal
 import socket
 import subprocess
@@ -27,23 +28,55 @@ def _free_port() -> int:
         return s.getsockname()[1]
 
 
+def _is_command(argv: list[str], module: bool) -> bool:
+    """``julia --project script.jl`` and friends are started as they are; anything else is a
+    Python script (or module) for this interpreter."""
+    if module or not argv:
+        return False
+    head = argv[0]
+    return not head.endswith(".py") and not os.path.isfile(head) and shutil.which(head) is not None
+
+
 def launch(nprocs: int, argv: list[str], timeout: float | None = None, module: bool = False,
-           env_extra: dict | None = None, capture: bool = False):
-    """Run ``argv`` N-way. Returns (exit_code, [stdout per rank] or None)."""
-    port = _free_port()
-    job = uuid.uuid4().hex[:12]
+           env_extra: dict | None = None, capture: bool = False, nnodes: int = 1,
+           node_rank: int = 0, master_addr: str = "127.0.0.1", master_port: int | None = None,
+           job_id: str | None = None, sim_nodes: int = 1):
+    """Run ``argv`` on ``nprocs`` ranks of this node. Returns (exit_code, [stdout per rank] or
+    None).
+
+    A job over several nodes starts one launcher per node with the same ``nnodes``,
+    ``master_addr`` (node 0's address) and ``master_port`` and its own ``node_rank``; global
+    ranks are node-major. ``sim_nodes=K`` splits the ranks of ONE machine into K pretend nodes
+    (shared memory inside each, TCP between them) so the multi-node paths can be tested anywhere.
+    """
+    if nnodes > 1 and (master_port is None or sim_nodes > 1):
+        raise ValueError("a multi-node job needs an explicit --master-port (the same on every node) "
+                         "and cannot be combined with --sim-nodes")
+    if sim_nodes < 1 or nprocs % sim_nodes:
+        raise ValueError(f"--sim-nodes {sim_nodes} does not divide -n {nprocs}")
+    port = master_port if master_port is not None else _free_port()
+    job = job_id or (f"mn{port}" if nnodes > 1 else uuid.uuid4().hex[:12])
+    lworld = nprocs // sim_nodes
+    world = nprocs * nnodes
+    as_command = _is_command(list(argv), module)
+    net_port = _free_port() if sim_nodes > 1 else None     # real jobs use MASTER_PORT + 1
     procs = []
     for r in range(nprocs):
         env = dict(os.environ)
+        grank = node_rank * nprocs + r
         env.update({
-            "RANK": str(r), "WORLD_SIZE": str(nprocs), "LOCAL_RANK": str(r),
-            "LOCAL_WORLD_SIZE": str(nprocs), "MASTER_ADDR": "127.0.0.1",
-            "MASTER_PORT": str(port), "FMPI_JOB_ID": job,
+            "RANK": str(grank), "WORLD_SIZE": str(world), "LOCAL_RANK": str(r % lworld),
+            "LOCAL_WORLD_SIZE": str(lworld), "GROUP_RANK": str(grank // lworld),
+            "MASTER_ADDR": master_addr, "MASTER_PORT": str(port), "FMPI_JOB_ID": job,
         })
+        if sim_nodes > 1:
+            env["FMPI_SIM_NODES"] = str(sim_nodes)
+            env["FMPI_NET_PORT"] = str(net_port)
         env.setdefault("OMP_NUM_THREADS", str(max(1, (os.cpu_count() or 1) // nprocs)))
         if env_extra:
             env.update({k: str(v) for k, v in env_extra.items()})
-        cmd = [sys.executable, "-u"] + (["-m"] if module else []) + list(argv)
+        cmd = list(argv) if as_command else \
+            [sys.executable, "-u"] + (["-m"] if module else []) + list(argv)
         out = subprocess.PIPE if capture else None
         procs.append(subprocess.Popen(cmd, env=env, stdout=out,
                                       stderr=subprocess.STDOUT if capture else None,
@@ -107,13 +140,22 @@ def _terminate(procs, which):
 def main(argv=None):
     ap = argparse.ArgumentParser(prog="python -m fluxmpi_b200.launch",
                                  description="start N SPMD ranks of a script")
-    ap.add_argument("-n", "--nprocs", type=int, required=True)
+    ap.add_argument("-n", "--nprocs", type=int, required=True, help="ranks on this node (one per GPU)")
     ap.add_argument("--timeout", type=float, default=None, help="seconds for the whole job")
     ap.add_argument("-m", dest="module", action="store_true", help="run a module (python -m)")
-    ap.add_argument("script")
+    ap.add_argument("--nnodes", type=int, default=1)
+    ap.add_argument("--node-rank", type=int, default=0)
+    ap.add_argument("--master-addr", default="127.0.0.1", help="address of node 0")
+    ap.add_argument("--master-port", type=int, default=None, help="same free port on every node")
+    ap.add_argument("--job-id", default=None, help="same on every node (default: from the port)")
+    ap.add_argument("--sim-nodes", type=int, default=1,
+                    help="testing: treat the ranks of this machine as this many nodes")
+    ap.add_argument("script", help="a .py file, a module with -m, or a command such as julia")
     ap.add_argument("args", nargs=argparse.REMAINDER)
     ns = ap.parse_args(argv)
-    code, _ = launch(ns.nprocs, [ns.script] + ns.args, timeout=ns.timeout, module=ns.module)
+    code, _ = launch(ns.nprocs, [ns.script] + ns.args, timeout=ns.timeout, module=ns.module,
+                     nnodes=ns.nnodes, node_rank=ns.node_rank, master_addr=ns.master_addr,
+                     master_port=ns.master_port, job_id=ns.job_id, sim_nodes=ns.sim_nodes)
     sys.exit(code)
 
 

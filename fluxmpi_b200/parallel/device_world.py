@@ -284,6 +284,12 @@ class DeviceWorld(_Base):
         if disabled and self.world > 1:
             self.why_fallback = "P2P support disabled by preference"
             return
+        if getattr(self, "nnodes", 1) > 1:
+            # peer mappings and multicast objects exist inside one NVSwitch domain only; a job
+            # that spans nodes sends its device tensors through NCCL (which is itself
+            # NVLink-inside / network-between) and its host tensors through the leader mesh
+            self.why_fallback = f"the job spans {self.nnodes} nodes and the NVLink kernels are node-local"
+            return
         try:
             need = self.sig_bytes + self.ar_bytes + self.bc_bytes
             if self.world == 1:
@@ -727,8 +733,9 @@ class DeviceWorld(_Base):
 
 
 def create(rank: int, world: int, device: int, job: str, disabled: bool = False,
-           window_bytes: Optional[int] = None, verbose: bool = False) -> DeviceWorld:
+           window_bytes: Optional[int] = None, verbose: bool = False, nnodes: int = 1) -> DeviceWorld:
     dw = DeviceWorld(rank, world, device, job)
+    dw.nnodes = nnodes
     dw.bring_up(disabled, verbose)
     if verbose:
         from .. import runtime

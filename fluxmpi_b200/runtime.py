@@ -53,6 +53,8 @@ class _State:
     world: int = 1
     local_rank: int = 0
     local_world: int = 1
+    node: int = 0
+    nnodes: int = 1
     device: Optional[torch.device] = None
     job: str = ""
     host_comm: Optional[int] = None           # fmpi_host_comm*
@@ -141,13 +143,33 @@ def Init(gpu_devices: Optional[Sequence[int]] = None, verbose: bool = False,
                              else os.environ.get("FMPI_TIMEOUT_S", 300.0))
         _S.job = _job_name()
 
+        if world % lworld or not (0 <= lrank < lworld):
+            raise ValueError(f"WORLD_SIZE={world} / LOCAL_WORLD_SIZE={lworld} / LOCAL_RANK={lrank}: "
+                             "every node must run the same number of ranks")
+        nnodes = world // lworld
+        node = _env_int("GROUP_RANK", rank // lworld)
+        if nnodes > 1 and rank != node * lworld + lrank:
+            raise ValueError(f"RANK={rank} is not node-major (node {node}, local rank {lrank} of {lworld})")
+        _S.node, _S.nnodes = node, nnodes
+
         if world > 1:
             lib = _native.host()
             h = C.c_void_p()
             name = ("/fmpi_" + "".join(ch if ch.isalnum() else "_" for ch in _S.job))[:200]
-            _native.host_check(
-                lib.fmpi_host_init(name.encode(), rank, world, slot_bytes, _S.timeout_s,
-                                   C.byref(h)), "fmpi_host_init")
+            if nnodes == 1:
+                _native.host_check(
+                    lib.fmpi_host_init(name.encode(), rank, world, slot_bytes, _S.timeout_s,
+                                       C.byref(h)), "fmpi_host_init")
+            else:
+                # shared memory inside the node, a TCP mesh between the node leaders
+                # (csrc/net_backend.cpp). The mesh port sits next to the rendezvous port the
+                # launcher handed out unless FMPI_NET_PORT says otherwise.
+                addr = os.environ.get("MASTER_ADDR", "127.0.0.1")
+                port = _env_int("FMPI_NET_PORT", _env_int("MASTER_PORT", 29500) + 1)
+                _native.host_check(
+                    lib.fmpi_host_init_multi(f"{name}_n{node}".encode(), lrank, lworld, node, nnodes,
+                                             addr.encode(), port, slot_bytes, _S.timeout_s,
+                                             C.byref(h)), "fmpi_host_init_multi")
             _S.host_comm = h.value
         # One worker => host collectives (blocking and non-blocking) execute in issue order.
         _S.host_pool = ThreadPoolExecutor(max_workers=1, thread_name_prefix="fmpi-host")
@@ -160,7 +182,8 @@ def Init(gpu_devices: Optional[Sequence[int]] = None, verbose: bool = False,
     if torch.cuda.is_available():
         ndev = torch.cuda.device_count()
         if gpu_devices is None:
-            dev = lrank % ndev
+            # pretend nodes (launch --sim-nodes) share one machine's GPUs: spread by global rank
+            dev = (rank if os.environ.get("FMPI_SIM_NODES") else lrank) % ndev
         else:
             dev = int(gpu_devices[rank])
         if verbose:
@@ -170,7 +193,7 @@ def Init(gpu_devices: Optional[Sequence[int]] = None, verbose: bool = False,
         from .parallel import device_world
         _S.device_world = device_world.create(
             rank=rank, world=world, device=dev, job=_S.job, disabled=_S.p2p_disabled,
-            window_bytes=device_window_bytes, verbose=verbose)
+            window_bytes=device_window_bytes, verbose=verbose, nnodes=_S.nnodes)
         _S.topology = _S.device_world.topology
         # one capability message per process, like the reference's load-time probe
         # (src/FluxMPI.jl:25-31: "CUDA-aware MPI support disabled" / "not CUDA Aware" / "is CUDA Aware")

@@ -91,6 +91,14 @@ _device_close(d::DeviceWorld) = ccall(csym(:fmpi_symm_destroy), Cint, (Ptr{Cvoid
 function _dev_allreduce!(v::CuArray{T}, op, root::Integer=-1; channel::Integer=0) where {T}
     w = WORLD[]
     (w.size == 1 || isempty(v)) && return v
+    if w.device === nothing
+        # P2P kernels switched off, or a job over several nodes: through host memory, the way
+        # the reference does without CUDA-aware MPI (src/mpi_extensions.jl:97-106)
+        h = Array(v)
+        out = root < 0 ? _host_allreduce!(h, op) : _host_reduce!(h, op, root)
+        (root < 0 || w.rank == root) && copyto!(v, out)
+        return v
+    end
     d = w.device::DeviceWorld
     p = Ref{Ptr{Cvoid}}(Base.unsafe_convert(Ptr{Cvoid}, pointer(v)))
     comm = Ref(d.comms[channel + 1])
@@ -110,6 +118,12 @@ end
 function _dev_bcast!(v::CuArray{T}, root::Integer; channel::Integer=0) where {T}
     w = WORLD[]
     (w.size == 1 || isempty(v)) && return v
+    if w.device === nothing                 # see _dev_allreduce!
+        h = Array(v)
+        _host_bcast!(h, root)
+        w.rank == root || copyto!(v, h)
+        return v
+    end
     d = w.device::DeviceWorld
     p = Ref{Ptr{Cvoid}}(Base.unsafe_convert(Ptr{Cvoid}, pointer(v)))
     ccheck(ccall(csym(:fmpi_bcast_any), Cint,

@@ -23,11 +23,23 @@ function _host_init()
     lrank = parse(Int, get(ENV, "LOCAL_RANK", string(rank)))
     job = _job_name()
     h = Ref{Ptr{Cvoid}}(C_NULL)
+    lsize = parse(Int, get(ENV, "LOCAL_WORLD_SIZE", string(size)))
+    nnodes = size ÷ lsize
     if size > 1
         name = "/fmpi_" * replace(job, r"[^A-Za-z0-9]" => "_")
         timeout = parse(Float64, get(ENV, "FMPI_TIMEOUT_S", "300"))
-        hcheck(ccall(hsym(:fmpi_host_init), Cint, (Cstring, Cint, Cint, Csize_t, Cdouble, Ptr{Ptr{Cvoid}}),
-                     name, rank, size, 8 << 20, timeout, h), "fmpi_host_init")
+        if nnodes == 1
+            hcheck(ccall(hsym(:fmpi_host_init), Cint, (Cstring, Cint, Cint, Csize_t, Cdouble, Ptr{Ptr{Cvoid}}),
+                         name, rank, size, 8 << 20, timeout, h), "fmpi_host_init")
+        else
+            # several nodes: shared memory inside each, a TCP mesh between the node leaders
+            node = parse(Int, get(ENV, "GROUP_RANK", string(rank ÷ lsize)))
+            port = parse(Int, get(ENV, "FMPI_NET_PORT", string(parse(Int, get(ENV, "MASTER_PORT", "29500")) + 1)))
+            hcheck(ccall(hsym(:fmpi_host_init_multi), Cint,
+                         (Cstring, Cint, Cint, Cint, Cint, Cstring, Cint, Csize_t, Cdouble, Ptr{Ptr{Cvoid}}),
+                         string(name, "_n", node), lrank, lsize, node, nnodes,
+                         get(ENV, "MASTER_ADDR", "127.0.0.1"), port, 8 << 20, timeout, h), "fmpi_host_init_multi")
+        end
     end
     WORLD[] = World(rank, size, lrank, h[], nothing, job)
     atexit(_finalize)

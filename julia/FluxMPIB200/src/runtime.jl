@@ -42,7 +42,12 @@ function Init(; gpu_devices::Union{Nothing, Vector{Int}}=nothing, verbose::Bool=
     dev = _pick_device(w, gpu_devices)
     verbose && fluxmpi_println("Using GPU $dev")
     CUDA.device!(dev)
-    @load_preference("FluxMPIDisableP2PSupport", false) || (w.device = _device_bringup(w, dev))
+    # peer mappings exist inside one NVSwitch domain; over several nodes CuArrays are staged
+    # through the host world (device.jl), like the reference without CUDA-aware MPI
+    one_node = parse(Int, get(ENV, "LOCAL_WORLD_SIZE", string(w.size))) == w.size
+    if one_node && !@load_preference("FluxMPIDisableP2PSupport", false)
+        w.device = _device_bringup(w, dev)
+    end
     return nothing
 end
 

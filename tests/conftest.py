@@ -22,14 +22,14 @@ def pytest_configure(config):
     _build.build_host()
 
 
-def run_spmd(script: str, nprocs: int, timeout: float = 180.0, env=None, args=()):
+def run_spmd(script: str, nprocs: int, timeout: float = 180.0, env=None, args=(), sim_nodes: int = 1):
     from fluxmpi_b200.launch import launch
     env_extra = {"PYTHONPATH": str(ROOT) + os.pathsep + os.environ.get("PYTHONPATH", ""),
                  "FMPI_TIMEOUT_S": "60"}
     if env:
         env_extra.update(env)
     code, outs = launch(nprocs, [str(ROOT / "tests" / "spmd" / script), *args], timeout=timeout,
-                        env_extra=env_extra, capture=True)
+                        env_extra=env_extra, capture=True, sim_nodes=sim_nodes)
     return code, outs
 
 
