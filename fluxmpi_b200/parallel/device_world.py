@@ -284,6 +284,9 @@ class DeviceWorld(_Base):
         if disabled and self.world > 1:
             self.why_fallback = "P2P support disabled by preference"
             return
+        if os.environ.get("FMPI_FORCE_FALLBACK", "0") not in ("0", ""):
+            self.why_fallback = "FMPI_FORCE_FALLBACK is set"     # A/B runs and tests, any world size
+            return
         if getattr(self, "nnodes", 1) > 1:
             # peer mappings and multicast objects exist inside one NVSwitch domain only; a job
             # that spans nodes sends its device tensors through NCCL (which is itself

@@ -23,6 +23,11 @@ What happens here:
 
 Rules without a fused kernel still work: the bucket is all-reduced in place by the two-shot
 kernel and the rule is applied with torch ops.
+
+Without peer mappings (``disable_p2p_support()``, ``FMPI_FORCE_FALLBACK=1``, a job over several
+nodes) the layout and the bucket schedule stay the same; a bucket is all-reduced by NCCL from
+the communication stream and the rule is applied by the local fused kernel, with the optimiser
+state replicated (tests/spmd/gpu_engine_fallback.py).
 """
 from __future__ import annotations
 
@@ -102,14 +107,27 @@ class DataParallelEngine:
         buf_bytes = (cur * es + (1 << 21) - 1) >> 21 << 21
 
         # ---- symmetric segment  [P | G]
-        if not self.native:
-            raise RuntimeError("DataParallelEngine needs the native device world; "
-                               f"fallback reason: {self.dw.why_fallback if self.dw else 'no device world'}")
-        self.seg = self.dw.alloc_segment(2 * buf_bytes)
         self.p_off, self.g_off = 0, buf_bytes
-        self.comm = self.dw.comm_for(self.seg, channel)
-        rawP = self.dw.symm_tensor(self.seg, self.p_off, cur * es)
-        rawG = self.dw.symm_tensor(self.seg, self.g_off, cur * es)
+        if self.native:
+            self.seg = self.dw.alloc_segment(2 * buf_bytes)
+            self.comm = self.dw.comm_for(self.seg, channel)
+            rawP = self.dw.symm_tensor(self.seg, self.p_off, cur * es)
+            rawG = self.dw.symm_tensor(self.seg, self.g_off, cur * es)
+        else:
+            # No peer mappings (P2P switched off, or the job spans nodes): the same flat layout
+            # in ordinary memory. A bucket is all-reduced by NCCL on the communication stream
+            # and the rule is then applied by the local fused kernel, still overlapping the rest
+            # of backward; the optimiser state is replicated, as in the reference.
+            if self.dw is None:
+                raise RuntimeError("DataParallelEngine needs Init() on a CUDA machine")
+            self.seg = None
+            self._flat = torch.empty(2 * buf_bytes, dtype=torch.uint8, device=self.device)
+            self.comm = _native.DevComm()           # a world of one over the flat buffer
+            self.comm.rank, self.comm.world, self.comm.emulate, self.comm.channel = 0, 1, 0, channel
+            self.comm.data[0] = self._flat.data_ptr()
+            self.comm.data_bytes = 2 * buf_bytes
+            rawP = self._flat[:cur * es]
+            rawG = self._flat[buf_bytes:buf_bytes + cur * es]
         self.P = rawP.view(self.dtype)
         self.G = rawG.view(self.dtype)
         self.G.zero_()
@@ -149,19 +167,20 @@ class DataParallelEngine:
             self.state_tree = None   # built lazily by the unfused path
 
         # in-switch reduction moves ~N bytes per link instead of 2N(W-1)/W: a win from W = 4 up
-        use_nvls = (algo == "nvls") or (algo == "auto" and bool(self.seg.mc_ptr) and self.world >= 4)
-        if algo == "nvls" and not self.seg.mc_ptr:
+        has_mc = self.native and bool(self.seg.mc_ptr)
+        use_nvls = (algo == "nvls") or (algo == "auto" and has_mc and self.world >= 4)
+        if algo == "nvls" and not has_mc:
             raise RuntimeError("algo='nvls' requested but this world has no multicast mapping")
         # measured choice for in-place all-reduce of a bucket-sized symmetric region, if any
         tuned = self.dw.tuner.choice("allreduce_symm", int(min(bucket_mb * (1 << 20), cur * es))) \
-            if (self.world > 1 and self.dw.tuner is not None) else None
+            if (self.native and self.world > 1 and self.dw.tuner is not None) else None
         if tuned is not None:
             if algo == "auto":
-                use_nvls = tuned[0] == "nvls" and bool(self.seg.mc_ptr)
+                use_nvls = tuned[0] == "nvls" and has_mc
         # CTA count: unlike a pure all-reduce (8-16 CTAs saturate the in-switch path) the fused
         # kernel also streams m, v and p through HBM; measured at 8 GPUs (bench/fused_bench.py)
         # 48 CTAs are 1.5-1.9x faster than 16 for both variants, so default well above that
-        if blocks == 0 and self.world > 1:
+        if blocks == 0 and self.world > 1 and self.native:
             self.blocks = int(os.environ.get("FMPI_FUSED_BLOCKS", 96))
         self.algo = _native.ALGO_NVLS if use_nvls else _native.ALGO_TWOSHOT
 
@@ -211,10 +230,13 @@ class DataParallelEngine:
         does the same with one MPI_Bcast of the flat vector) + buffers through the tree path."""
         lib = _native.cuda()
         nbytes = self.numel * self.P.element_size()
-        cuda_check(lib.fmpi_bcast_symm(C.byref(self.comm), self.p_off, nbytes, root,
-                                       C.byref(Launch(0, 0, 0)), torch.cuda.current_stream().cuda_stream),
-                   "bcast_symm")
-        _native.count_launch()
+        if self.native:
+            cuda_check(lib.fmpi_bcast_symm(C.byref(self.comm), self.p_off, nbytes, root,
+                                           C.byref(Launch(0, 0, 0)), torch.cuda.current_stream().cuda_stream),
+                       "bcast_symm")
+            _native.count_launch()
+        elif self.world > 1:
+            self.dw._nccl().broadcast(self.P, root)
         if self.master is not None:
             self.master.copy_(self.P)
         bufs = [b for b in self.module.buffers() if b.numel() > 0]
@@ -272,6 +294,11 @@ class DataParallelEngine:
             stream.wait_stream(cur)      # the bucket's gradients are complete on `cur`
             self._armed = True
         lib = _native.cuda()
+        if not self.native and self.world > 1:
+            # NCCL runs on its own stream; issuing from `stream` makes it start after the
+            # bucket's gradients and makes `stream` (not the host) wait for the result
+            with torch.cuda.stream(stream):
+                self.dw._nccl().all_reduce(self.G[b.lo:b.hi])
         if self.fused:
             one = lambda t: C.byref(C.c_void_p(t.data_ptr())) if t is not None else None
             step_ptr = C.byref(C.c_void_p(self.step_dev.data_ptr()))
@@ -283,7 +310,7 @@ class DataParallelEngine:
         else:
             code = F._dtype_code(self.dtype)
             es = self.G.element_size()
-            if self.world > 1:
+            if self.world > 1 and self.native:
                 cuda_check(lib.fmpi_allreduce_symm(
                     C.byref(self.comm), self.g_off + b.lo * es, b.hi - b.lo, code, _native.SUM,
                     C.byref(Launch(self.blocks, 0, 0)), stream.cuda_stream), "allreduce_symm")
@@ -335,6 +362,8 @@ class DataParallelEngine:
     # ------------------------------------------------------------------ state access
     def owned_ranges(self) -> list[tuple[int, int]]:
         """Element ranges whose optimiser state this rank owns (one slice per bucket)."""
+        if not self.native:                 # replicated state: every rank holds all of it
+            return [(b.lo, b.hi) for b in self.buckets]
         es = self.P.element_size()
         n_per_vec = 16 // es
         out = []
@@ -356,6 +385,9 @@ class DataParallelEngine:
         for name in ("m", "v", "master"):
             t = getattr(self, name)
             if t is None:
+                continue
+            if not self.native:
+                out[name] = t.clone()
                 continue
             full = torch.zeros_like(t)
             for lo, hi in self.owned_ranges():

@@ -47,3 +47,13 @@ def test_chunk_pipelined_large_message_path():
 
 def test_nccl_fallback_when_p2p_disabled():
     _run("gpu_collectives.py", 2, env={"FMPI_DISABLE_P2P": "1"}, args=("quick",))
+
+
+def test_engine_without_peer_mappings_over_nccl():
+    """profiles/runs/fallback_engine_2gpu.log"""
+    _run("gpu_engine_fallback.py", 2, env={"FMPI_FORCE_FALLBACK": "1"})
+
+
+def test_pretend_nodes_device_tensors_take_nccl():
+    """2 pretend nodes x 1 GPU: host world over the TCP mesh, device collectives over NCCL."""
+    _run("gpu_collectives.py", 2, args=("quick",), sim_nodes=2)
