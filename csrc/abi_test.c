@@ -71,8 +71,34 @@ static int run_rank(const char* name, int rank, int world, int nodes, int port) 
   for (int r = 0; r < world; ++r)
     if (all[r] != 100 + r) return 7;
 
+  /* three arrays as one message (pieces straddle the 64 KB slots) */
+  enum { NA = 5, NB = 30000, NC = 1 };
+  double *ta = malloc(sizeof(double) * NA), *tb = malloc(sizeof(double) * NB), tc[NC] = {rank + 1.0};
+  for (int i = 0; i < NA; ++i) ta[i] = rank + 1.0;
+  for (int i = 0; i < NB; ++i) tb[i] = (rank + 1.0) * (i % 7);
+  void* leaves[3] = {ta, tb, tc};
+  const uint64_t counts[3] = {NA, NB, NC};
+  CHECK(fmpi_host_allreduce_many(c, 3, leaves, counts, FMPI_F64, FMPI_SUM));
+  const double tri = world * (world + 1) / 2.0;
+  for (int i = 0; i < NB; ++i)
+    if (tb[i] != tri * (i % 7)) { fprintf(stderr, "rank %d: allreduce_many wrong at %d\n", rank, i); return 8; }
+  if (ta[NA - 1] != tri || tc[0] != tri) return 9;
+
+  /* the rule loop: x -= eta * g over two leaves */
+  float p1[3] = {1, 1, 1}, p2[1] = {4}, g1[3] = {2, 2, 2}, g2[1] = {8};
+  void* ps[2] = {p1, p2};
+  const void* gs[2] = {g1, g2};
+  const uint64_t ns[2] = {3, 1};
+  const double hyper[7] = {0.5, 0.9, 0.999, 1e-8, 0.0, 0.0, 1.0};
+  CHECK(fmpi_host_multi_tensor_step(2, ps, gs, NULL, NULL, ns, FMPI_F32, FMPI_RULE_DESCENT, hyper, 0));
+  if (p1[2] != 0.0f || p2[0] != 0.0f) return 10;
+  if (fmpi_host_multi_tensor_step(2, ps, gs, NULL, NULL, ns, FMPI_F32, FMPI_RULE_ADAM, hyper, 0) == 0)
+    return 11; /* Adam without moment arrays must be refused */
+
   CHECK(fmpi_host_barrier(c));
   CHECK(fmpi_host_finalize(c));
+  free(ta);
+  free(tb);
   free(x);
   free(all);
   return 0;

@@ -66,16 +66,19 @@ double now_s() {
   return double(ts.tv_sec) + 1e-9 * double(ts.tv_nsec);
 }
 
-// Spin a little, then yield, then sleep: ranks are usually oversubscribed on CPU test boxes.
+// Waiting policy: spin (a peer that is running arrives within microseconds), then yield the
+// core (ranks may outnumber cores on CPU test boxes), then sleep in short naps so a job that
+// waits for a long time does not burn a core per rank. A nap costs 50+ us of latency, so it is
+// kept for waits that are already long.
 struct Backoff {
   int n = 0;
   void pause() {
     ++n;
-    if (n < 64) {
+    if (n < 1024) {
 #if defined(__x86_64__)
       __builtin_ia32_pause();
 #endif
-    } else if (n < 512) {
+    } else if (n < 1024 + 8192) {
       sched_yield();
     } else {
       timespec ts{0, 50000};
@@ -472,6 +475,58 @@ int fmpi_host_allreduce(fmpi_host_comm* c, const void* send, void* recv, size_t 
     memcpy(d + done * es, c->result, n * es);
   }
   // The result slot must stay intact until everyone has copied it out.
+  return c->barrier();
+}
+
+// The leaves of a gradient tree as ONE message: pieces are copied from the leaves straight
+// into the staging slot and from the result slot straight back, so a tree costs the barriers of
+// one message and no intermediate flat copy (the reference sends one MPI message per leaf,
+// src/optimizer.jl:55-58).
+int fmpi_host_allreduce_many(fmpi_host_comm* c, int n, void* const* bufs, const uint64_t* counts,
+                             int dtype, int op) {
+  if (!c) return fail("null communicator");
+  const size_t es = dtype_size(dtype);
+  if (es == 0) return fail("unsupported dtype %d", dtype);
+  if (op < FMPI_SUM || op > FMPI_MAX) return fail("unsupported op %d", op);
+  if (n < 0 || (n > 0 && (!bufs || !counts))) return fail("fmpi_host_allreduce_many: bad arguments");
+  if ((c->world == 1 && c->nnodes == 1) || n == 0) return 0;
+  size_t total = 0;
+  for (int k = 0; k < n; ++k) total += counts[k];
+  const size_t chunk = c->slot_bytes / es;
+  uint8_t* mine = c->slots + size_t(c->rank) * c->slot_bytes;
+  int leaf = 0;       // first leaf that still has elements at or after `done`
+  size_t leaf_lo = 0; // index of that leaf's first element in the concatenation
+  for (size_t done = 0; done < total; done += chunk) {
+    const size_t m = total - done < chunk ? total - done : chunk;
+    while (leaf < n && leaf_lo + counts[leaf] <= done) leaf_lo += counts[leaf++];
+    // walk the leaves overlapping [done, done + m) twice: copy in, then copy out
+    for (int pass = 0; pass < 2; ++pass) {
+      int k = leaf;
+      size_t klo = leaf_lo;
+      while (k < n && klo < done + m) {
+        const size_t a = klo > done ? klo : done;
+        const size_t kend = klo + counts[k];
+        const size_t b = kend < done + m ? kend : done + m;
+        if (b > a) {
+          uint8_t* user = static_cast<uint8_t*>(bufs[k]) + (a - klo) * es;
+          if (pass == 0) memcpy(mine + (a - done) * es, user, (b - a) * es);
+          else memcpy(user, c->result + (a - done) * es, (b - a) * es);
+        }
+        klo = kend;
+        ++k;
+      }
+      if (pass == 1) break;
+      if (c->barrier()) return 1;
+      const size_t per = (m + size_t(c->world) - 1) / size_t(c->world);
+      const size_t lo = per * size_t(c->rank) < m ? per * size_t(c->rank) : m;
+      const size_t hi = lo + per < m ? lo + per : m;
+      if (hi > lo) reduce_dispatch(dtype, c->slots, c->slot_bytes, c->world, c->result, lo, hi, op);
+      if (c->barrier()) return 1;
+      if (c->nnodes > 1 &&
+          c->leader_phase(c->net ? fmpi_net_allreduce(c->net, c->result, m, dtype, op) : 0))
+        return 1;
+    }
+  }
   return c->barrier();
 }
 

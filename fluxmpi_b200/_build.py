@@ -22,7 +22,7 @@ CSRC = ROOT / "csrc"
 INC = ROOT / "include"
 LIB = Path(__file__).resolve().parent / "_lib"
 
-HOST_SOURCES = ["host_backend.cpp", "fdx.cpp", "net_backend.cpp"]
+HOST_SOURCES = ["host_backend.cpp", "fdx.cpp", "net_backend.cpp", "host_rules.cpp"]
 CUDA_SOURCES = [
     "symm.cpp",
     "topo.cpp",
@@ -95,7 +95,10 @@ def build_host(force: bool = False, verbose: bool = False) -> Path:
         if not force and not _stale(out, srcs, _headers()):
             return out
         tmp = out.with_suffix(f".so.tmp{os.getpid()}")
-        cmd = ["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-pthread",
+        # -O3 for the loop vectoriser; no FMA contraction so every ISA clone of the rule loops
+        # (csrc/host_rules.cpp) rounds the same way and replicas on different CPUs stay equal
+        # (-fno-math-errno: sqrt without the errno branch, or the Adam loop stays scalar)
+        cmd = ["g++", "-O3", "-ffp-contract=off", "-fno-math-errno", "-std=c++17", "-fPIC", "-shared", "-Wall", "-pthread",
                f"-I{INC}", *map(str, srcs), "-o", str(tmp), "-lrt"]
         if verbose:
             print(" ".join(cmd), file=sys.stderr)

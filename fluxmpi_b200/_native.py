@@ -94,6 +94,11 @@ def host():
                                         C.c_int]
         lib.fmpi_net_bcast.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]
         lib.fmpi_net_allgather.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+        lib.fmpi_host_allreduce_many.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                                 C.c_int, C.c_int]
+        lib.fmpi_host_multi_tensor_step.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+                                                    C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                                    C.c_void_p, C.c_int64]
         _host = lib
     return _host
 

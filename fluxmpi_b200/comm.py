@@ -18,6 +18,7 @@ ignored (there is one world, like the reference's hard-coded ``MPI.COMM_WORLD``)
 """
 from __future__ import annotations
 
+import ctypes as C
 from concurrent.futures import Future
 from typing import Optional
 
@@ -138,6 +139,20 @@ def _host_allreduce_now(send: torch.Tensor, recv: torch.Tensor, op: int):
         recv.copy_(r)
 
 
+def _host_allreduce_many_now(ts, op: int):
+    """All contiguous CPU tensors of one dtype, reduced in place as one message."""
+    S = runtime.state()
+    if S.world == 1 or not ts:
+        return
+    n = len(ts)
+    ptrs, counts = (C.c_void_p * n)(), (C.c_uint64 * n)()
+    for i, t in enumerate(ts):
+        ptrs[i], counts[i] = t.data_ptr(), t.numel()
+    _native.host_check(
+        _native.host().fmpi_host_allreduce_many(S.host_comm, n, ptrs, counts,
+                                                dtype_code(ts[0].dtype), op), "allreduce_many")
+
+
 def _host_bcast_now(buf: torch.Tensor, root: int):
     S = runtime.state()
     if S.world == 1:
@@ -193,7 +208,7 @@ def allreduce_(v, op="sum", comm=COMM_WORLD):
     if t.is_cuda:
         _device_world().allreduce(t, code)
     else:
-        runtime.host_submit(_host_allreduce_now, t, t, code).result()
+        runtime.host_run(_host_allreduce_now, t, t, code)
     return v
 
 
@@ -206,7 +221,7 @@ def bcast_(v, root: int = 0, comm=COMM_WORLD):
     if t.is_cuda:
         _device_world().bcast(t, root)
     else:
-        runtime.host_submit(_host_bcast_now, t, root).result()
+        runtime.host_run(_host_bcast_now, t, root)
     return v
 
 
@@ -221,7 +236,7 @@ def reduce_(v, op="sum", root: int = 0, comm=COMM_WORLD):
     if t.is_cuda:
         _device_world().reduce(t, code, root)
     else:
-        runtime.host_submit(_host_reduce_now, t, t, code, root).result()
+        runtime.host_run(_host_reduce_now, t, t, code, root)
     return v
 
 

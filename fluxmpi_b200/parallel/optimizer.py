@@ -112,6 +112,12 @@ def allreduce_gradients(gs, on_gpu: bool | None = None):
             if dw is not None and dw.native:
                 dw.allreduce_many(ts, comm.op_code("sum"))
                 continue
+        if dev.type == "cpu" and all(t.is_contiguous() for t in ts):
+            # the leaves are copied straight into / out of the shared-memory slots: one message,
+            # no flattening copy (csrc/host_backend.cpp fmpi_host_allreduce_many)
+            runtime.host_run(comm._host_allreduce_many_now,
+                             [t.detach() if t.requires_grad else t for t in ts], comm.op_code("sum"))
+            continue
         if len(ts) == 1:
             _, req = comm.Iallreduce(ts[0], "sum")
             reqs.append(req)

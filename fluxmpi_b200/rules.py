@@ -388,6 +388,11 @@ def walk_update(state_tree, params, grads, inplace: bool):
         from .ops import fused
         if fused.try_tree_step_(state_tree, params, grads):
             return state_tree, params
+    elif inplace:
+        # CPU leaves: the same idea, one native call and one pass over memory per leaf
+        from .ops import host_rules
+        if host_rules.try_tree_step_host_(state_tree, params, grads):
+            return state_tree, params
     return _walk_update(state_tree, params, grads, inplace, {})
 
 

@@ -64,6 +64,8 @@ class _State:
     topology: dict = field(default_factory=dict)
     timeout_s: float = 300.0
     lock: threading.Lock = field(default_factory=threading.Lock)
+    host_exec: threading.Lock = field(default_factory=threading.Lock)   # one host collective at a time
+    host_pending: int = 0                     # non-blocking host collectives not yet finished
 
 
 _S = _State()
@@ -269,11 +271,36 @@ def state() -> _State:
 # ---------------------------------------------------------------------------- host helpers
 
 
+def _host_done(_fut):
+    _S.host_pending -= 1
+
+
 def host_submit(fn, *args):
-    """Run ``fn`` on the single host-communication worker (keeps collective order)."""
+    """Queue ``fn`` on the single host-communication worker (non-blocking collectives; keeps
+    issue order). Returns the future."""
     if not _S.initialized:
         raise FluxMPINotInitializedError()
-    return _S.host_pool.submit(fn, *args)
+
+    def run():
+        with _S.host_exec:
+            return fn(*args)
+
+    _S.host_pending += 1
+    fut = _S.host_pool.submit(run)
+    fut.add_done_callback(_host_done)
+    return fut
+
+
+def host_run(fn, *args):
+    """Run a blocking host collective. With nothing queued it runs on the calling thread (a
+    hand-over to the worker and back costs more than a small shared-memory all-reduce);
+    otherwise it takes its place behind the non-blocking calls already issued."""
+    if not _S.initialized:
+        raise FluxMPINotInitializedError()
+    if _S.host_pending > 0:
+        return host_submit(fn, *args).result()
+    with _S.host_exec:
+        return fn(*args)
 
 
 def _host_barrier_now():
@@ -287,7 +314,7 @@ def host_barrier():
     if not _S.initialized:
         raise FluxMPINotInitializedError()
     if _S.world > 1:
-        host_submit(_host_barrier_now).result()
+        host_run(_host_barrier_now)
 
 
 def host_allgather_bytes(blob: bytes, size: Optional[int] = None) -> list[bytes]:
@@ -305,7 +332,7 @@ def host_allgather_bytes(blob: bytes, size: Optional[int] = None) -> list[bytes]
         raw = recv.raw
         return [raw[i * n:(i + 1) * n] for i in range(_S.world)]
 
-    return host_submit(run).result()
+    return host_run(run)
 
 
 # ---------------------------------------------------------------------------- printing

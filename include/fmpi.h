@@ -50,6 +50,18 @@ typedef enum {
   FMPI_RULE_ADAMW = 4      /* Adam then x -= lambda*x (OptimiserChain(Adam, WeightDecay)) */
 } fmpi_rule;
 
+/* Hyper-parameter block of the fused rule kernels (fmpi_fused_step, fmpi_multi_tensor_step).
+ * 48 bytes. */
+typedef struct {
+  int32_t rule;          /* fmpi_rule */
+  float eta, beta1, beta2, eps, lambda, rho;
+  float grad_scale;      /* multiplies the summed gradient (1 = reference SUM semantics) */
+  int32_t zero_grad;     /* != 0: each rank clears its gradient bucket after the end barrier
+                            (fused device step only) */
+  uint64_t eta_dev;      /* optional device pointer to a float that overrides eta (learning-rate
+                            schedules under CUDA-graph replay); 0 = use eta. Device only. */
+} fmpi_hyper;
+
 /* ------------------------------------------------------------------ host backend */
 
 typedef struct fmpi_host_comm fmpi_host_comm;
@@ -69,6 +81,10 @@ int fmpi_host_barrier(fmpi_host_comm* c);
  * slice reduces in rank order 0..W-1). */
 int fmpi_host_allreduce(fmpi_host_comm* c, const void* send, void* recv, size_t count,
                         int dtype, int op);
+/* In-place all-reduce of n separate arrays of one dtype as a single message (a gradient tree):
+ * the barriers of one message, no flattening copy. */
+int fmpi_host_allreduce_many(fmpi_host_comm* c, int n, void* const* bufs, const uint64_t* counts,
+                             int dtype, int op);
 int fmpi_host_bcast(fmpi_host_comm* c, void* buf, size_t nbytes, int root);
 /* Only root's recv is written; non-root buffers are left untouched
  * (test/test_mpi_extensions.jl:56-60). */
@@ -76,6 +92,18 @@ int fmpi_host_reduce(fmpi_host_comm* c, const void* send, void* recv, size_t cou
                      int op, int root);
 /* all-gather of equal-sized blobs (handle exchange, print ordering, tests) */
 int fmpi_host_allgather(fmpi_host_comm* c, const void* send, void* recv, size_t nbytes_each);
+
+/* Optimiser rule over a table of n host tensors in one call, one pass over memory per leaf
+ * (the CPU twin of fmpi_multi_tensor_step; the reference leaves this to Optimisers.jl's
+ * per-leaf broadcasts, src/optimizer.jl:20-25). p and g have dtype `dtype` (FMPI_F32 or
+ * FMPI_F64), m and v are arrays of the same dtype (entries may be NULL when the rule does not
+ * use them). hyper = {eta, beta1, beta2, eps, lambda, rho, grad_scale} in double so fp64
+ * tensors lose nothing. `step` = completed steps so far (bias correction uses step + 1).
+ * Arithmetic is done in the tensors' own precision, in the operation order of rules.py, so the
+ * result matches the per-leaf path to rounding. */
+int fmpi_host_multi_tensor_step(int n, void* const* p, const void* const* g, void* const* m,
+                                void* const* v, const uint64_t* numel, int dtype, int rule,
+                                const double* hyper, int64_t step);
 
 /* Unix-domain-socket file-descriptor exchange (SCM_RIGHTS), used to pass CUDA VMM
  * shareable handles between the ranks of one node. */
@@ -210,15 +238,8 @@ int fmpi_barrier_dev(const fmpi_devcomm* c, fmpi_stream st);
  * replicas stay bit-identical. Moments m, v (fp32) and the optional fp32 master copy are
  * process-local arrays indexed like the window (only the owned slice is touched).
  * step_dev points at a device int64 holding the number of completed steps (read only; advance
- * it with fmpi_step_advance so CUDA-graph replays see fresh bias corrections). */
-typedef struct {
-  int32_t rule;          /* fmpi_rule */
-  float eta, beta1, beta2, eps, lambda, rho;
-  float grad_scale;      /* multiplies the summed gradient (1 = reference SUM semantics) */
-  int32_t zero_grad;     /* != 0: each rank clears its gradient bucket after the end barrier */
-  uint64_t eta_dev;      /* optional device pointer to a float that overrides eta (learning-rate
-                            schedules under CUDA-graph replay); 0 = use eta */
-} fmpi_hyper;
+ * it with fmpi_step_advance so CUDA-graph replays see fresh bias corrections).
+ * Hyper-parameters: fmpi_hyper, defined with the rules at the top of this header. */
 
 int fmpi_fused_step(const fmpi_devcomm* c, uint64_t g_off, int gdt, uint64_t p_off, int pdt,
                     float* const* m, float* const* v, float* const* master,

@@ -29,13 +29,21 @@ flat vector — is accepted too.
 """
 function allreduce_gradients(gs::Union{NamedTuple, Tuple}; on_gpu::Bool=CUDA.functional())
     pending = Request[]
+    host = Dict{DataType, Vector{Any}}()      # host leaves by eltype: one message per eltype
     post(leaf) = leaf
+    function post(leaf::Array{T}) where {T <: Union{Float32, Float64, Float16, Int32, Int64, Int16, Int8, UInt8}}
+        push!(get!(host, T, Any[]), leaf)
+        return leaf
+    end
     function post(leaf::AbstractArray{<:Number})
         out, req = Iallreduce!(leaf, +)
         push!(pending, req)
         return out
     end
     reduced = fmap(post, gs)
+    for (T, leaves) in host
+        _host_allreduce_many!(Vector{Array{T}}(leaves), +)
+    end
     waitall(pending)
     return reduced
 end

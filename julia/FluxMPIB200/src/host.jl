@@ -78,6 +78,21 @@ function _host_allreduce!(v::Array{T}, op) where {T}
     return v
 end
 
+# A whole gradient tree as one shared-memory message: pieces go from the leaves straight into
+# the staging slot and back (no flattening copy, the barriers of a single message).
+function _host_allreduce_many!(leaves::Vector{<:Array{T}}, op) where {T}
+    w = WORLD[]
+    (w.size == 1 || isempty(leaves)) && return leaves
+    ptrs = Ptr{Cvoid}[Base.unsafe_convert(Ptr{Cvoid}, pointer(l)) for l in leaves]
+    counts = UInt64[length(l) for l in leaves]
+    GC.@preserve leaves begin
+        hcheck(ccall(hsym(:fmpi_host_allreduce_many), Cint,
+                     (Ptr{Cvoid}, Cint, Ptr{Ptr{Cvoid}}, Ptr{UInt64}, Cint, Cint),
+                     w.host, length(leaves), ptrs, counts, dtype_code(T), op_code(op)), "allreduce_many")
+    end
+    return leaves
+end
+
 function _host_bcast!(v::Array{T}, root::Integer) where {T}
     w = WORLD[]
     w.size == 1 && return v

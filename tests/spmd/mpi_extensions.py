@@ -71,6 +71,18 @@ for dt in (torch.float32, torch.float64, torch.float16, torch.bfloat16, torch.in
             fm.allreduce_(chk, "max")
             assert all(torch.equal(chk[q], out) for q in range(w)), (dt, n, op, "replica drift")
 
+# a gradient tree as ONE message: leaves of odd sizes that straddle the 64 KB slots, compared
+# bit for bit with one all-reduce per leaf
+for dt in (torch.float32, torch.float64):
+    tree = {"a": torch.rand(3, generator=gen).to(dt), "b": [torch.rand(20011, generator=gen).to(dt),
+            torch.rand(1, generator=gen).to(dt)], "c": {"w": torch.rand(130, 257, generator=gen).to(dt)},
+            "note": "not an array"}
+    ref = [fm.allreduce_(t.clone(), "sum") for t in (tree["a"], *tree["b"], tree["c"]["w"])]
+    out = fm.allreduce_gradients(tree)
+    got = (out["a"], *out["b"], out["c"]["w"])
+    assert all(torch.equal(g, x) for g, x in zip(got, ref)), dt
+    assert out["note"] == "not an array"
+
 # bcast from every root, reduce to every root, big payload
 for root in range(w):
     t = torch.full((33333,), float(r))

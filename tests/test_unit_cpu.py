@@ -141,6 +141,43 @@ def test_update_inplace_mutates_and_adjust():
     assert st["w"].rule.optimizer.eta == 1e-2
 
 
+@pytest.mark.parametrize("dt", [torch.float32, torch.float64])
+@pytest.mark.parametrize("rule", [R.Descent(0.1), R.Momentum(0.01, 0.9), R.Nesterov(0.01, 0.9),
+                                  R.Adam(1e-3), R.AdamW(1e-3, (0.9, 0.99), 1e-3)],
+                         ids=["descent", "momentum", "nesterov", "adam", "adamw"])
+def test_native_host_rule_loop_matches_per_leaf_ops(rule, dt):
+    """``update_`` on CPU leaves is one native call (csrc/host_rules.cpp); same numbers as the
+    per-leaf array operations to the last bit or two, tied leaves stepped once, state in place."""
+    import copy
+    from fluxmpi_b200.ops import host_rules
+    torch.manual_seed(0)
+    ps = {"a": torch.randn(257, 33, dtype=dt), "b": {"w": torch.randn(1000, dtype=dt), "k": 3}}
+    ps["b"]["tied"] = ps["b"]["w"]
+    ps2 = copy.deepcopy(ps)
+    ps2["b"]["tied"] = ps2["b"]["w"]
+    st, st2 = R.setup(rule, ps), R.setup(rule, ps2)
+    m0 = st["a"].state[0] if isinstance(st["a"].state, tuple) and isinstance(st["a"].state[0], torch.Tensor) else None
+    for _ in range(6):
+        gs = {"a": torch.randn(257, 33, dtype=dt), "b": {"w": torch.randn(1000, dtype=dt), "k": None}}
+        gs["b"]["tied"] = gs["b"]["w"]
+        assert host_rules.try_tree_step_host_(st, ps, gs)            # the native path qualifies
+        st2, ps2 = R._walk_update(st2, ps2, gs, True, {})             # per-leaf torch ops
+    eps = 4 * torch.finfo(dt).eps
+    for a, b in ((ps["a"], ps2["a"]), (ps["b"]["w"], ps2["b"]["w"])):
+        assert torch.allclose(a, b, rtol=eps, atol=eps), float((a - b).abs().max())
+    assert ps["b"]["tied"] is ps["b"]["w"] and ps["b"]["k"] == 3
+    assert T.tree_equal(st["a"].state[2] if m0 is not None else None,
+                        st2["a"].state[2] if m0 is not None else None)   # same bias-correction powers
+    if m0 is not None:
+        assert st["a"].state[0] is m0                                   # moments updated in place
+    # a rule without a native loop, or a non-contiguous leaf, declines and changes nothing
+    before = ps["a"].clone()
+    assert not host_rules.try_tree_step_host_(R.setup(R.RMSProp(), ps), ps, gs)
+    pt = {"w": torch.randn(8, 6, dtype=dt).t()}
+    assert not host_rules.try_tree_step_host_(R.setup(rule, pt), pt, {"w": torch.ones(6, 8, dtype=dt)})
+    assert torch.equal(ps["a"], before)
+
+
 def test_distributed_optimizer_state_equals_inner_rule():
     """test/test_optimizer.jl:13-14 — without any world."""
     ps = {"a": torch.zeros(4), "b": torch.zeros(4)}
