@@ -65,6 +65,7 @@ class _State:
     timeout_s: float = 300.0
     lock: threading.Lock = field(default_factory=threading.Lock)
     host_exec: threading.Lock = field(default_factory=threading.Lock)   # one host collective at a time
+    host_count: threading.Lock = field(default_factory=threading.Lock)  # guards host_pending
     host_pending: int = 0                     # non-blocking host collectives not yet finished
 
 
@@ -175,6 +176,7 @@ def Init(gpu_devices: Optional[Sequence[int]] = None, verbose: bool = False,
             _S.host_comm = h.value
         # One worker => host collectives (blocking and non-blocking) execute in issue order.
         _S.host_pool = ThreadPoolExecutor(max_workers=1, thread_name_prefix="fmpi-host")
+        _S.host_pending = 0
         _S.initialized = True
 
     if verbose and world == 1:
@@ -272,7 +274,8 @@ def state() -> _State:
 
 
 def _host_done(_fut):
-    _S.host_pending -= 1
+    with _S.host_count:               # the callback runs on the worker thread
+        _S.host_pending -= 1
 
 
 def host_submit(fn, *args):
@@ -285,7 +288,8 @@ def host_submit(fn, *args):
         with _S.host_exec:
             return fn(*args)
 
-    _S.host_pending += 1
+    with _S.host_count:
+        _S.host_pending += 1
     fut = _S.host_pool.submit(run)
     fut.add_done_callback(_host_done)
     return fut

@@ -83,6 +83,24 @@ for dt in (torch.float32, torch.float64):
     assert all(torch.equal(g, x) for g, x in zip(got, ref)), dt
     assert out["note"] == "not an array"
 
+# blocking calls issued while non-blocking ones are still in flight keep their place in line on
+# every rank (ranks are skewed on purpose so some find the queue empty and others do not)
+import random
+import time
+rnd = random.Random(r)
+for it in range(60):
+    big = torch.full((50000,), float(r + it))
+    small = torch.full((3,), float(r))
+    _, req = fm.Iallreduce(big, big, "sum")
+    if rnd.random() < 0.5:
+        time.sleep(rnd.random() * 2e-3)
+    fm.allreduce_(small, "max")                       # must not overtake the queued one
+    _, req2 = fm.Ibcast(small, it % w)
+    fm.barrier()
+    req.wait(); req2.wait()
+    assert torch.equal(big, torch.full((50000,), float(sum(range(w)) + w * it))), it
+    assert torch.equal(small, torch.full((3,), float(w - 1))), it
+
 # bcast from every root, reduce to every root, big payload
 for root in range(w):
     t = torch.full((33333,), float(r))
