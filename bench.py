@@ -14,6 +14,8 @@ Arms (--impl):
              image has no Julia and no MPI, so the arm reports {"unavailable": ...}.
   ddp        the operative baseline named by BASELINE.json's fallback: torch DDP + NCCL +
              torch.optim.Adam(fused=True), same model / dtype / input pipeline, stock eager path.
+  refshape   the reference's step shape on this box's software (SURVEY §6 "reference-shaped"):
+             per leaf D2H, blocking host all-reduce, H2D, then the rule as per-leaf array ops.
 
 One JSON line on rank 0. `value` = whole-job images/s over the device-timed steps (CUDA events,
 max over ranks); `e2e` = the same through the public API with a pinned-host→device copy of every
@@ -39,7 +41,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "ddp"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "ddp", "refshape"])
     ap.add_argument("--model", default="resnet50", choices=["resnet50", "resnet_tiny"])
     ap.add_argument("--batch", type=int, default=256, help="per-GPU batch (weak scaling)")
     ap.add_argument("--image", type=int, default=224)
@@ -417,6 +419,85 @@ def run_ddp(a):
         dist.destroy_process_group()
 
 
+def run_refshape(a):
+    """B-REFSHAPE: the reference's step *shape* on this box's software — after the
+    whole backward pass, for every parameter leaf: gradient D2H, blocking host all-reduce, H2D
+    (what its CuArray wrappers do as written, src/mpi_extensions.jl:97-106), then the rule as
+    per-leaf array operations (src/optimizer.jl:20-23). Host collectives are this library's
+    shared-memory backend standing in for MPI; nothing is fused, bucketed, overlapped or graphed."""
+    import torch
+    import fluxmpi_b200 as fm
+    from fluxmpi_b200 import rules as R
+
+    torch.backends.cudnn.benchmark = True
+    fm.Init()
+    rank, world = fm.local_rank(), fm.total_workers()
+    assert world == a.gpus, f"--gpus {a.gpus} but WORLD_SIZE={world}"
+    dev = fm.current_device()
+    cdt = torch.bfloat16 if a.dtype == "bf16" else torch.float32
+    torch.manual_seed(0)
+    model = make_model(a.model).to(dev).to(memory_format=torch.channels_last)
+    model = fm.synchronize(fm.FluxMPIFluxModel(model), root_rank=0)
+    ps = dict(model.named_parameters())
+    st = R.setup(R.Adam(1e-3), ps)
+
+    def do_step(xb, yb):
+        nonlocal st
+        x = preprocess(xb, torch.float32)
+        with torch.autocast("cuda", dtype=cdt, enabled=a.dtype == "bf16"):
+            loss = torch.nn.functional.cross_entropy(model(x), yb)
+        for p in ps.values():
+            p.grad = None
+        loss.backward()
+        gs = {}
+        for k, p in ps.items():                       # one blocking, host-staged message per leaf
+            h = p.grad.cpu()
+            fm.allreduce_(h, "sum")
+            gs[k] = h.to(dev)
+        st, _ = R._walk_update(st, ps, gs, True, {})  # per-leaf array ops
+        return loss
+
+    nb = 4
+    hx, hy = host_dataset(nb, a.batch, a.image, seed=1000 + rank)
+    hx, hy = hx.pin_memory(), hy.pin_memory()
+    loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+    for i in range(max(a.warmup, 3)):
+        do_step(hx[:a.batch].to(dev), hy[:a.batch].to(dev))
+    torch.cuda.synchronize()
+
+    def e2e_steps(k):
+        for i in range(k):
+            s = i % nb
+            xb = hx[s * a.batch:(s + 1) * a.batch].to(dev, non_blocking=True)
+            yb = hy[s * a.batch:(s + 1) * a.batch].to(dev, non_blocking=True)
+            loss = do_step(xb, yb)
+            loss_host.copy_(loss.detach().float().reshape(1), non_blocking=True)
+        torch.cuda.synchronize()
+
+    sampler = ClockSampler(dev.index) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    ms = timed(e2e_steps, a.steps, fm.barrier, "ours")
+    clocks = sampler.stop() if sampler else None
+    gb = a.batch * world
+    value = gb * a.steps / (ms / 1e3)
+    if rank == 0:
+        print(json.dumps({
+            "metric": "ResNet-50 train images/s (synthetic 224x224, data-parallel)", "impl": "refshape",
+            "value": round(value, 1), "unit": "img/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": round(ms / a.steps, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": a.dtype, "data": "synthetic",
+            "config": {"model": a.model, "global_batch": gb, "per_gpu_batch": a.batch, "image": a.image,
+                       "parallelism": f"dp{world}", "optimizer": "Adam as per-leaf array ops",
+                       "layout": "channels_last",
+                       "comm": "per leaf: D2H, blocking shared-memory host all-reduce, H2D (reference shape)"},
+            "e2e": {"value": round(value, 1), "unit": "img/s",
+                    "h2d_bytes_per_step": int(a.batch * (a.image * a.image * 3 + 8)), "d2h_bytes_per_step": 4,
+                    "note": "the timed region is the end-to-end loop; gradient staging traffic not counted here"},
+            "gpu_launches": 0, "final_loss": float(loss_host[0]), "clocks": clocks}))
+    fm.Finalize()
+
+
 def run_reference(a):
     if int(os.environ.get("RANK", "0")) == 0:
         print(json.dumps({
@@ -428,4 +509,5 @@ def run_reference(a):
 
 if __name__ == "__main__":
     args = parse()
-    {"ours": run_ours, "ddp": run_ddp, "reference": run_reference}[args.impl](args)
+    {"ours": run_ours, "ddp": run_ddp, "reference": run_reference,
+     "refshape": run_refshape}[args.impl](args)
