@@ -215,6 +215,7 @@ def cuda():
         lib.fmpi_bn_scratch_bytes.argtypes = [i32]
         lib.fmpi_bn_scratch_bytes.restype = C.c_size_t
         lib.fmpi_bn_forward.argtypes = [vp, vp, vp, u64, i32, i32, vp, vp, vp, vp, f32, f32, i32, vp, vp, vp, vp]
+        lib.fmpi_bn_forward_presummed.argtypes = list(lib.fmpi_bn_forward.argtypes)
         lib.fmpi_bn_apply.argtypes = [vp, vp, vp, u64, i32, i32, vp, vp, i32, vp]
         lib.fmpi_bn_backward.argtypes = [vp, vp, vp, vp, vp, u64, i32, i32, vp, vp, vp, vp, vp, i32, vp, vp]
         lib.fmpi_maxpool_fwd.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]

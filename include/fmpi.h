@@ -304,6 +304,24 @@ int fmpi_bn_backward(const void* dy, const void* y, const void* x, void* dx, voi
                      const float* save_invstd, float* dgamma, float* dbeta, int relu, void* scratch,
                      fmpi_stream st);
 
+/* forward without the statistics pass: the first 2*C floats of scratch already hold the
+ * per-channel sum and sum of squares of x (left there by fmpi_conv1x1_bnstats). */
+int fmpi_bn_forward_presummed(const void* x, const void* res, void* y, uint64_t M, int C, int dtype,
+                              const float* gamma, const float* beta, float* running_mean,
+                              float* running_var, float momentum, float eps, int relu,
+                              float* save_mean, float* save_invstd, void* scratch, fmpi_stream st);
+
+/* ---- 1x1 convolution on channels-last activations as a tcgen05 GEMM with the BatchNorm
+ * statistics in its epilogue (csrc/kernels/gemm_bnstats.cu; a separate library,
+ * libfmpi_gemm.so, because it is built from the CUTLASS header tree):
+ *   y[M, N] = x[M, K] * w[N, K]^T  (bf16, row-major; N and K multiples of 8)
+ *   sum[N], sqs[N] (fp32) = column sums of the fp32 accumulators and of their squares.
+ * EXPERIMENTAL: compiled and inspected, not yet run on a GPU; nothing uses it by default. */
+size_t fmpi_conv1x1_bnstats_workspace(int M, int N, int K);
+int fmpi_conv1x1_bnstats(const void* x, const void* w, void* y, float* sum, float* sqs, int M, int N,
+                         int K, void* workspace, size_t workspace_bytes, fmpi_stream st);
+const char* fmpi_gemm_last_error(void);
+
 /* ---- channels-last max pooling (csrc/kernels/pool.cu): x [N,H,W,C] -> y [N,OH,OW,C] with
  * OH = (H + 2P - K)/S + 1; idx keeps one byte per output element (window position of the
  * maximum) for the atomics-free gather backward. */

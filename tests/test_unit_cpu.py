@@ -300,6 +300,13 @@ def test_fused_ops_fall_back_to_stock_ops_off_gpu():
     img = torch.randn(2, 3, 32, 32)
     assert torch.allclose(a(img), b(img), atol=1e-5)
     assert sum(p.numel() for p in a.parameters()) == sum(p.numel() for p in b.parameters())
+    # the conv + BN-statistics fusion (ops/conv_bn.py) declines off GPU and changes nothing
+    c = resnet_tiny(fused_bn=True, fused_conv_bn=True)
+    c.load_state_dict(a.state_dict())
+    assert c.layer1[0].fused_conv_bn and list(c.state_dict()) == list(a.state_dict())
+    assert torch.allclose(c(img), a(img), atol=1e-6)
+    (c(img).sum()).backward()
+    assert c.layer1[0].conv1.weight.grad is not None
 
 
 def test_device_loader_cpu_shuffle_and_remainder():
