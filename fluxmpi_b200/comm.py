@@ -195,15 +195,76 @@ def _device_world():
 # ------------------------------------------------------------------------------ blocking API
 
 
+def _resolve_op(op):
+    """(native op code, None) for sum / prod / min / max in any spelling, else (None, callable):
+    the reference accepts any Julia function and wraps it in ``MPI.Op``
+    (src/mpi_extensions.jl:52-54); an arbitrary Python callable ``f(a, b) -> tensor`` takes the
+    gather-and-fold path below."""
+    try:
+        return op_code(op), None
+    except ValueError:
+        if callable(op):
+            return None, op
+        raise
+
+
+def _host_custom_now(send: torch.Tensor, recv: torch.Tensor, fn, root: int):
+    """Reduction with a user function: all-gather the operands, fold them in rank order on
+    every rank (same order everywhere, hence the same bits). ``root < 0`` = all ranks keep the
+    result. W copies of the message live on each rank while this runs: meant for the odd custom
+    reduction, not for gradients."""
+    S = runtime.state()
+    s, _ = _host_view(send)
+    if S.world == 1:
+        if recv.data_ptr() != s.data_ptr():
+            recv.copy_(s)
+        return
+    raw = s.reshape(-1).view(torch.uint8) if s.dtype != torch.bool else s.reshape(-1).to(torch.uint8)
+    n, W = raw.numel(), S.world
+    parts = torch.empty(W, n, dtype=torch.uint8)
+    chunk = max(1, S.slot_bytes // W)
+    tmp = torch.empty(W * chunk, dtype=torch.uint8)
+    lib = _native.host()
+    for off in range(0, n, chunk):
+        m = min(chunk, n - off)
+        _native.host_check(lib.fmpi_host_allgather(S.host_comm, raw.data_ptr() + off, tmp.data_ptr(), m),
+                           "allgather")
+        parts[:, off:off + m] = tmp[:W * m].view(W, m)
+    if root >= 0 and S.rank != root:
+        return
+    vals = [p.view(s.dtype).view(s.shape) if s.dtype != torch.bool else p.bool().view(s.shape) for p in parts]
+    acc = vals[0]
+    for x in vals[1:]:
+        acc = fn(acc, x)
+    with torch.no_grad():
+        recv.copy_(torch.as_tensor(acc).reshape(recv.shape))
+
+
+def _custom(send: torch.Tensor, recv: torch.Tensor, fn, root: int = -1):
+    if recv.is_cuda:                       # staged through the host, as the reference's MPI would
+        h = send.detach().cpu()
+        out = h.clone()
+        runtime.host_run(_host_custom_now, h, out, fn, root)
+        if root < 0 or runtime.local_rank() == root:
+            with torch.no_grad():
+                recv.copy_(out)
+    else:
+        runtime.host_run(_host_custom_now, send.detach(), recv.detach(), fn, root)
+
+
 def allreduce_(v, op="sum", comm=COMM_WORLD):
     """In-place all-reduce of ``v`` with ``op``; returns ``v``.
 
     CPU tensors / numpy arrays: POSIX-shm backend. CUDA tensors: NVLink P2P kernel enqueued on
-    the current stream (stream-ordered, like every torch op)."""
+    the current stream (stream-ordered, like every torch op). ``op`` may also be any callable
+    ``f(a, b)`` on tensors (gathered and folded in rank order)."""
     if not runtime.Initialized():
         raise runtime.FluxMPINotInitializedError()
     t = _as_tensor(v)
-    code = op_code(op)
+    code, fn = _resolve_op(op)
+    if fn is not None:
+        _custom(t, t, fn)
+        return v
     dtype_code(t.dtype)
     if t.is_cuda:
         _device_world().allreduce(t, code)
@@ -230,8 +291,11 @@ def reduce_(v, op="sum", root: int = 0, comm=COMM_WORLD):
     if not runtime.Initialized():
         raise runtime.FluxMPINotInitializedError()
     t = _as_tensor(v)
-    code = op_code(op)
+    code, fn = _resolve_op(op)
     _check_root(root)
+    if fn is not None:
+        _custom(t, t, fn, root)
+        return v
     dtype_code(t.dtype)
     if t.is_cuda:
         _device_world().reduce(t, code, root)
@@ -266,7 +330,13 @@ def Iallreduce(*args, comm=COMM_WORLD):
         raise TypeError("Iallreduce(send, recv, op) or Iallreduce(buf, op)")
     s, r = _as_tensor(send), _as_tensor(recv)
     _check_pair(s, r)
-    code = op_code(op)
+    code, fn = _resolve_op(op)
+    if fn is not None:                      # custom function: host path, queued like the others
+        if r.is_cuda:
+            _custom(s, r, fn)
+            return recv, Request(buffer=recv)
+        fut = runtime.host_submit(_host_custom_now, s.detach(), r.detach(), fn, -1)
+        return recv, Request(future=fut, buffer=recv)
     dtype_code(s.dtype)
     if r.is_cuda:
         ev = _device_world().allreduce_async(s, r, code)

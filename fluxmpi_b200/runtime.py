@@ -63,6 +63,7 @@ class _State:
     p2p_disabled: bool = False
     topology: dict = field(default_factory=dict)
     timeout_s: float = 300.0
+    slot_bytes: int = 8 << 20                 # staging slot of the host world
     lock: threading.Lock = field(default_factory=threading.Lock)
     host_exec: threading.Lock = field(default_factory=threading.Lock)   # one host collective at a time
     host_count: threading.Lock = field(default_factory=threading.Lock)  # guards host_pending
@@ -144,6 +145,7 @@ def Init(gpu_devices: Optional[Sequence[int]] = None, verbose: bool = False,
         _S.rank, _S.world, _S.local_rank, _S.local_world = rank, world, lrank, lworld
         _S.timeout_s = float(timeout_s if timeout_s is not None
                              else os.environ.get("FMPI_TIMEOUT_S", 300.0))
+        _S.slot_bytes = (int(slot_bytes) + 63) & ~63 or (4 << 20)
         _S.job = _job_name()
 
         if world % lworld or not (0 <= lrank < lworld):

@@ -91,9 +91,10 @@ _device_close(d::DeviceWorld) = ccall(csym(:fmpi_symm_destroy), Cint, (Ptr{Cvoid
 function _dev_allreduce!(v::CuArray{T}, op, root::Integer=-1; channel::Integer=0) where {T}
     w = WORLD[]
     (w.size == 1 || isempty(v)) && return v
-    if w.device === nothing
-        # P2P kernels switched off, or a job over several nodes: through host memory, the way
-        # the reference does without CUDA-aware MPI (src/mpi_extensions.jl:97-106)
+    if w.device === nothing || !(op isa NativeOp)
+        # P2P kernels switched off, a job over several nodes, or a custom reduction function:
+        # through host memory, the way the reference does without CUDA-aware MPI
+        # (src/mpi_extensions.jl:97-106)
         h = Array(v)
         out = root < 0 ? _host_allreduce!(h, op) : _host_reduce!(h, op, root)
         (root < 0 || w.rank == root) && copyto!(v, out)

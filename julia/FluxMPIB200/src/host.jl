@@ -70,7 +70,35 @@ function host_allgather(blob::Vector{UInt8})
     return [out[(i * length(blob) + 1):((i + 1) * length(blob))] for i in 0:(w.size - 1)]
 end
 
-function _host_allreduce!(v::Array{T}, op) where {T}
+const NativeOp = Union{typeof(+), typeof(*), typeof(min), typeof(max)}
+
+# Any other function (the reference wraps it in MPI.Op, src/mpi_extensions.jl:52-54): gather
+# every rank's array in slot-sized pieces and fold them in rank order — the same order on every
+# rank, so the result is identical everywhere even for non-commutative functions.
+function _host_fold!(v::Array{T}, f, root::Integer=-1) where {T}
+    w = WORLD[]
+    w.size == 1 && return v
+    isbitstype(T) || throw(FluxMPIError("custom reductions need a bits eltype, got $T"))
+    mine = collect(reinterpret(UInt8, vec(v)))
+    n = length(mine)
+    parts = [Vector{UInt8}(undef, n) for _ in 1:w.size]
+    chunk = max(1, (8 << 20) ÷ w.size)
+    for lo in 1:chunk:n
+        hi = min(lo + chunk - 1, n)
+        got = host_allgather(mine[lo:hi])
+        for q in 1:w.size
+            parts[q][lo:hi] = got[q]
+        end
+    end
+    (root >= 0 && w.rank != root) && return v
+    vals = [reshape(collect(reinterpret(T, p)), size(v)) for p in parts]
+    copyto!(v, foldl((a, b) -> f.(a, b), vals))
+    return v
+end
+
+_host_allreduce!(v::Array, f) = _host_fold!(v, f)
+
+function _host_allreduce!(v::Array{T}, op::NativeOp) where {T}
     w = WORLD[]
     w.size == 1 && return v
     hcheck(ccall(hsym(:fmpi_host_allreduce), Cint, (Ptr{Cvoid}, Ptr{T}, Ptr{T}, Csize_t, Cint, Cint),
@@ -101,7 +129,9 @@ function _host_bcast!(v::Array{T}, root::Integer) where {T}
     return v
 end
 
-function _host_reduce!(v::Array{T}, op, root::Integer) where {T}
+_host_reduce!(v::Array, f, root::Integer) = _host_fold!(v, f, root)
+
+function _host_reduce!(v::Array{T}, op::NativeOp, root::Integer) where {T}
     w = WORLD[]
     w.size == 1 && return v
     hcheck(ccall(hsym(:fmpi_host_reduce), Cint, (Ptr{Cvoid}, Ptr{T}, Ptr{T}, Csize_t, Cint, Cint, Cint),

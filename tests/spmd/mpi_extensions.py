@@ -71,6 +71,30 @@ for dt in (torch.float32, torch.float64, torch.float16, torch.bfloat16, torch.in
             fm.allreduce_(chk, "max")
             assert all(torch.equal(chk[q], out) for q in range(w)), (dt, n, op, "replica drift")
 
+# any function as the reduction (the reference wraps a Julia function in MPI.Op,
+# src/mpi_extensions.jl:52-54): folded in rank order, so non-commutative ones are well defined
+t = torch.full((70001,), float(r + 1), dtype=torch.float64)         # larger than a 64 KB slot
+fm.allreduce_(t, lambda a, b: 2 * a + b)
+want = 1.0
+for q in range(1, w):
+    want = 2 * want + (q + 1)
+assert torch.equal(t, torch.full((70001,), want, dtype=torch.float64)), (float(t[0]), want)
+t = torch.tensor([r, -r, 7], dtype=torch.int64)
+fm.reduce_(t, torch.maximum, w - 1)                                  # a torch function, to a root
+assert torch.equal(t, torch.tensor([w - 1, 0, 7]) if r == w - 1 else torch.tensor([r, -r, 7]))
+a, b = torch.full((5,), float(r)), torch.zeros(5)
+_, req = fm.Iallreduce(a, b, lambda x, y: x - y)
+req.wait()
+want = 0.0
+for q in range(1, w):
+    want = want - q
+assert torch.equal(b, torch.full((5,), want)) and torch.equal(a, torch.full((5,), float(r)))
+try:
+    fm.allreduce_(torch.ones(2), "median")
+    raise AssertionError("unknown op name accepted")
+except ValueError:
+    pass
+
 # a gradient tree as ONE message: leaves of odd sizes that straddle the 64 KB slots, compared
 # bit for bit with one all-reduce per leaf
 for dt in (torch.float32, torch.float64):
