@@ -150,13 +150,38 @@ def main(argv=None):
     ap.add_argument("--job-id", default=None, help="same on every node (default: from the port)")
     ap.add_argument("--sim-nodes", type=int, default=1,
                     help="testing: treat the ranks of this machine as this many nodes")
+    ap.add_argument("--max-restarts", type=int, default=0,
+                    help="single-node jobs: start all ranks again (up to this many times) when one "
+                         "fails; the script sees FMPI_RESTART_COUNT and resumes from its checkpoint")
     ap.add_argument("script", help="a .py file, a module with -m, or a command such as julia")
     ap.add_argument("args", nargs=argparse.REMAINDER)
     ns = ap.parse_args(argv)
-    code, _ = launch(ns.nprocs, [ns.script] + ns.args, timeout=ns.timeout, module=ns.module,
-                     nnodes=ns.nnodes, node_rank=ns.node_rank, master_addr=ns.master_addr,
-                     master_port=ns.master_port, job_id=ns.job_id, sim_nodes=ns.sim_nodes)
+    if ns.max_restarts and ns.nnodes > 1:
+        ap.error("--max-restarts needs all ranks under one launcher (single node)")
+    code = run_with_restarts(ns.nprocs, [ns.script] + ns.args, ns.max_restarts, timeout=ns.timeout,
+                             module=ns.module, nnodes=ns.nnodes, node_rank=ns.node_rank,
+                             master_addr=ns.master_addr, master_port=ns.master_port, job_id=ns.job_id,
+                             sim_nodes=ns.sim_nodes)
     sys.exit(code)
+
+
+def run_with_restarts(nprocs: int, argv: list[str], max_restarts: int = 0, **kw) -> int:
+    """Failure handling one step beyond detection (the reference has neither): when
+    a rank dies the job is torn down — that part is ``launch`` — and, if restarts are allowed,
+    started again as a whole with ``FMPI_RESTART_COUNT`` = attempt number, so a script that
+    checkpoints (``fm.checkpoint``) continues from its last save. A timeout (exit 124) is not
+    retried."""
+    extra = dict(kw.pop("env_extra", None) or {})
+    code = 0
+    for attempt in range(max_restarts + 1):
+        extra["FMPI_RESTART_COUNT"] = attempt
+        code, _ = launch(nprocs, argv, env_extra=extra, **kw)
+        if code in (0, 124):
+            break
+        if attempt < max_restarts:
+            print(f"[fluxmpi_b200.launch] job failed with exit code {code}; restart "
+                  f"{attempt + 1} of {max_restarts}", file=sys.stderr, flush=True)
+    return code
 
 
 if __name__ == "__main__":

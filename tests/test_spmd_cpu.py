@@ -60,6 +60,18 @@ def test_checkpoint_roundtrip_and_trace(spmd, tmp_path):
     assert all(f"RANK_OK {r}" in o for r, o in enumerate(outs))
 
 
+def test_job_restarts_and_resumes_from_checkpoint(tmp_path):
+    """launch --max-restarts: the job that lost a rank is started again as a whole and the
+    script continues from its last checkpoint (tests/spmd/restart.py asserts where it resumed)."""
+    import os
+    from conftest import ROOT
+    from fluxmpi_b200.launch import run_with_restarts
+    env = {"PYTHONPATH": str(ROOT) + os.pathsep + os.environ.get("PYTHONPATH", ""), "FMPI_TIMEOUT_S": "60"}
+    script = str(ROOT / "tests" / "spmd" / "restart.py")
+    assert run_with_restarts(3, [script, str(tmp_path / "a.pt")], 0, timeout=120, env_extra=env) == 7
+    assert run_with_restarts(3, [script, str(tmp_path / "b.pt")], 1, timeout=240, env_extra=env) == 0
+
+
 def test_dead_rank_is_detected(spmd):
     """A rank that dies must not leave the others hanging (the reference has no such guard,
     SURVEY §5): the launcher kills the job and reports the failing exit code."""
