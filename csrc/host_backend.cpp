@@ -277,15 +277,24 @@ struct fmpi_host_comm {
     return 0;
   }
 
-  // Every rank of the node calls this after the leader ran its inter-node step (rc = what that
-  // step returned; 0 on the other ranks). A failed leader poisons the node so the ranks waiting
-  // for it give up too; otherwise the node meets and may read what the leader brought back.
+  // Every rank of the node calls this after its inter-node step (rc = what that step returned;
+  // 0 for a rank that had nothing to send). A failure poisons the node so the ranks waiting at
+  // the barrier give up too; otherwise the node meets and may read what came back.
   int leader_phase(int rc) {
     if (rc) {
       if (hdr) hdr->aborted.store(1, std::memory_order_relaxed);
       return 1;
     }
     return barrier();
+  }
+
+  // Slice [lo, hi) of a chunk of n units that this rank owns: it reduces that slice inside the
+  // node and it is the one that carries it between nodes — local rank l of every node forms
+  // "rail" l with its own sockets, so a node's network traffic is spread over all of its ranks.
+  void my_slice(size_t n, size_t* lo, size_t* hi) const {
+    const size_t per = (n + size_t(world) - 1) / size_t(world);
+    *lo = per * size_t(rank) < n ? per * size_t(rank) : n;
+    *hi = *lo + per < n ? *lo + per : n;
   }
 };
 
@@ -422,14 +431,19 @@ int fmpi_host_init_multi(const char* name, int local_rank, int local_world, int 
   }
   c->node = node;
   c->nnodes = nnodes;
-  if (nnodes > 1 && local_rank == 0) {
-    if (fmpi_net_init(master_addr, port, node, nnodes, c->timeout_s, &c->net)) {
+  if (nnodes > 1) {
+    // one mesh per rail: local rank l of every node, rendezvous on port + l of node 0
+    if (port + local_world - 1 > 65535) {
+      fmpi_host_finalize(c);
+      return fail("ports %d..%d are out of range", port, port + local_world - 1);
+    }
+    if (fmpi_net_init(master_addr, port + local_rank, node, nnodes, c->timeout_s, &c->net)) {
       if (c->hdr) c->hdr->aborted.store(1, std::memory_order_relaxed);
       fmpi_host_finalize(c);
       return 1;
     }
   }
-  // nobody leaves before its leader is connected, so the first collective cannot race the mesh
+  // nobody leaves before every rail of the node is connected
   if (c->barrier()) { fmpi_host_finalize(c); return 1; }
   *out = c;
   return 0;
@@ -442,7 +456,7 @@ int fmpi_host_barrier(fmpi_host_comm* c) {
   if (!c) return fail("null communicator");
   if (c->barrier()) return 1;
   if (c->nnodes == 1) return 0;
-  if (c->leader_phase(c->net ? fmpi_net_barrier(c->net) : 0)) return 1;
+  if (c->leader_phase(c->rank == 0 ? fmpi_net_barrier(c->net) : 0)) return 1;   // rail 0 only
   return 0;
 }
 
@@ -468,9 +482,10 @@ int fmpi_host_allreduce(fmpi_host_comm* c, const void* send, void* recv, size_t 
     const size_t hi = lo + per < n ? lo + per : n;
     if (hi > lo) reduce_dispatch(dtype, c->slots, c->slot_bytes, c->world, c->result, lo, hi, op);
     if (c->barrier()) return 1;
-    // the node's sum now sits in the result slot; the leader folds in the other nodes'
+    // the node's sum now sits in the result slot; every rank folds the other nodes' into the
+    // slice it owns, over its own rail
     if (c->nnodes > 1 &&
-        c->leader_phase(c->net ? fmpi_net_allreduce(c->net, c->result, n, dtype, op) : 0))
+        c->leader_phase(hi > lo ? fmpi_net_allreduce(c->net, c->result + lo * es, hi - lo, dtype, op) : 0))
       return 1;
     memcpy(d + done * es, c->result, n * es);
   }
@@ -523,7 +538,7 @@ int fmpi_host_allreduce_many(fmpi_host_comm* c, int n, void* const* bufs, const 
       if (hi > lo) reduce_dispatch(dtype, c->slots, c->slot_bytes, c->world, c->result, lo, hi, op);
       if (c->barrier()) return 1;
       if (c->nnodes > 1 &&
-          c->leader_phase(c->net ? fmpi_net_allreduce(c->net, c->result, m, dtype, op) : 0))
+          c->leader_phase(hi > lo ? fmpi_net_allreduce(c->net, c->result + lo * es, hi - lo, dtype, op) : 0))
         return 1;
     }
   }
@@ -556,7 +571,7 @@ int fmpi_host_reduce(fmpi_host_comm* c, const void* send, void* recv, size_t cou
     if (hi > lo) reduce_dispatch(dtype, c->slots, c->slot_bytes, c->world, c->result, lo, hi, op);
     if (c->barrier()) return 1;
     if (c->nnodes > 1 &&
-        c->leader_phase(c->net ? fmpi_net_reduce(c->net, c->result, n, dtype, op, root_node) : 0))
+        c->leader_phase(hi > lo ? fmpi_net_reduce(c->net, c->result + lo * es, hi - lo, dtype, op, root_node) : 0))
       return 1;
     if (is_root) memcpy(d + done * es, c->result, n * es);
   }
@@ -574,9 +589,11 @@ int fmpi_host_bcast(fmpi_host_comm* c, void* buf, size_t nbytes, int root) {
     const size_t n = nbytes - done < c->slot_bytes ? nbytes - done : c->slot_bytes;
     if (is_root) memcpy(c->result, b + done, n);
     if (c->barrier()) return 1;
-    if (c->nnodes > 1 &&
-        c->leader_phase(c->net ? fmpi_net_bcast(c->net, c->result, n, root_node) : 0))
-      return 1;
+    if (c->nnodes > 1) {   // each rail carries its slice of the chunk from the root's node
+      size_t lo, hi;
+      c->my_slice(n, &lo, &hi);
+      if (c->leader_phase(hi > lo ? fmpi_net_bcast(c->net, c->result + lo, hi - lo, root_node) : 0)) return 1;
+    }
     if (!is_root) memcpy(b + done, c->result, n);
     if (c->barrier()) return 1;
   }
@@ -602,7 +619,7 @@ int fmpi_host_allgather(fmpi_host_comm* c, const void* send, void* recv, size_t 
     memcpy(c->result + size_t(c->node) * node_bytes + size_t(c->rank) * nbytes_each, send,
            nbytes_each);
     if (c->barrier()) return 1;
-    if (c->leader_phase(c->net ? fmpi_net_allgather(c->net, c->result + size_t(c->node) * node_bytes,
+    if (c->leader_phase(c->rank == 0 ? fmpi_net_allgather(c->net, c->result + size_t(c->node) * node_bytes,
                                                     c->result, node_bytes)
                                : 0))
       return 1;

@@ -1,8 +1,9 @@
-// Leader mesh: host collectives between the nodes of a job, over TCP.
+// Rail mesh: host collectives between the nodes of a job, over TCP.
 //
 // The reference reaches other nodes through whatever fabric its MPI was built for (SURVEY §2.2,
-// "Multi-node: implicitly, via whatever mpiexec launches"). This image has no MPI, so the one
-// rank per node that leads it (local rank 0) keeps a socket to every other leader and the few
+// "Multi-node: implicitly, via whatever mpiexec launches"). This image has no MPI, so local
+// rank l of every node keeps a socket to local rank l of every other node (one such mesh per
+// rail, csrc/host_backend.cpp hands each rail its slice of a chunk) and the few
 // collectives the host world needs are written on top of one primitive, `exchange`, which
 // progresses any number of sends and receives at once with poll(2): nobody can dead-lock on a
 // full socket buffer and every wait is bounded by the job's timeout.

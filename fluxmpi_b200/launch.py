@@ -28,6 +28,28 @@ def _free_port() -> int:
         return s.getsockname()[1]
 
 
+def _free_port_range(k: int) -> int:
+    """First port of k consecutive free ones (the rails of a multi-node host world use
+    base .. base + ranks_per_node - 1)."""
+    for _ in range(200):
+        base = _free_port()
+        if base + k > 65535:
+            continue
+        socks = []
+        try:
+            for p in range(base, base + k):
+                s = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
+                socks.append(s)
+                s.bind(("0.0.0.0", p))
+            return base
+        except OSError:
+            continue
+        finally:
+            for s in socks:
+                s.close()
+    raise RuntimeError(f"no {k} consecutive free ports found")
+
+
 def _is_command(argv: list[str], module: bool) -> bool:
     """``julia --project script.jl`` and friends are started as they are; anything else is a
     Python script (or module) for this interpreter."""
@@ -59,7 +81,8 @@ def launch(nprocs: int, argv: list[str], timeout: float | None = None, module: b
     lworld = nprocs // sim_nodes
     world = nprocs * nnodes
     as_command = _is_command(list(argv), module)
-    net_port = _free_port() if sim_nodes > 1 else None     # real jobs use MASTER_PORT + 1
+    # real jobs use MASTER_PORT + 1 .. MASTER_PORT + ranks_per_node (one rail per local rank)
+    net_port = _free_port_range(nprocs // sim_nodes) if sim_nodes > 1 else None
     procs = []
     for r in range(nprocs):
         env = dict(os.environ)

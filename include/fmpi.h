@@ -119,14 +119,15 @@ int fmpi_fdx_close(int sock, const char* job, int rank);
 const char* fmpi_fdx_last_error(void);
 
 /* ---- more than one node (csrc/net_backend.cpp) --------------------------------------------
- * The reference spans nodes through whatever `mpiexec` starts. Here one rank per
- * node (local rank 0, the "leader") joins a full TCP mesh with the other leaders; the ranks of
- * a node keep talking through shared memory. Global rank = node * local_world + local_rank
- * (every node runs the same number of ranks).
+ * The reference spans nodes through whatever `mpiexec` starts. Here the ranks of
+ * a node keep talking through shared memory and local rank l of every node joins a full TCP
+ * mesh with the other nodes' local rank l ("rail" l), which carries slice l of every chunk.
+ * Global rank = node * local_world + local_rank (every node runs the same number of ranks).
  *
- * fmpi_net_*: collectives between leaders, in place. Node 0 listens on master_addr:port for
- * the rendezvous; the others dial in (retrying until timeout_s). Reductions are done by one
- * owner per slice in node order, so every node ends with the same bits. */
+ * fmpi_net_*: collectives between the members of one mesh (one per node), in place. Node 0
+ * listens on master_addr:port for the rendezvous; the others dial in (retrying until
+ * timeout_s). Reductions are done by one owner per slice in node order, so every node ends
+ * with the same bits. */
 typedef struct fmpi_net fmpi_net;
 int fmpi_net_init(const char* master_addr, int port, int node, int nnodes, double timeout_s,
                   fmpi_net** out);
@@ -138,9 +139,10 @@ int fmpi_net_reduce(fmpi_net* n, void* buf, size_t count, int dtype, int op, int
 int fmpi_net_bcast(fmpi_net* n, void* buf, size_t nbytes, int root_node);
 int fmpi_net_allgather(fmpi_net* n, const void* send, void* recv, size_t nbytes_each);
 
-/* Two-level host world: shared memory inside the node + the leader mesh between nodes. The
- * returned communicator is used with the same fmpi_host_* calls as a single-node one; ranks and
- * roots are global. `name` must differ between nodes that share a machine (tests). */
+/* Two-level host world: shared memory inside the node + one mesh per rail between nodes (local
+ * rank l rendezvouses on port + l of node 0). The returned communicator is used with the same
+ * fmpi_host_* calls as a single-node one; ranks and roots are global. `name` must differ
+ * between nodes that share a machine (tests). */
 int fmpi_host_init_multi(const char* name, int local_rank, int local_world, int node, int nnodes,
                          const char* master_addr, int port, size_t slot_bytes, double timeout_s,
                          fmpi_host_comm** out);

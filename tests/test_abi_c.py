@@ -11,10 +11,9 @@ LIB = ROOT / "fluxmpi_b200" / "_lib"
 
 
 def _free_port():
-    import socket
-    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as s:
-        s.bind(("127.0.0.1", 0))
-        return s.getsockname()[1]
+    """Base of a run of free ports: a multi-node host world uses one port per local rank."""
+    from fluxmpi_b200.launch import _free_port_range
+    return _free_port_range(8)
 
 
 # (world, nodes): nodes > 1 goes through fmpi_host_init_multi (shared memory + TCP leader mesh)

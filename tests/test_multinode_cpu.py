@@ -38,9 +38,9 @@ def test_quickstart_over_two_nodes():
 
 
 def _free_port():
-    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as s:
-        s.bind(("127.0.0.1", 0))
-        return s.getsockname()[1]
+    """MASTER_PORT with the ports behind it free too (rails use MASTER_PORT + 1 ...)."""
+    from fluxmpi_b200.launch import _free_port_range
+    return _free_port_range(8)
 
 
 def _two_launchers(script, per_node, args=(), timeout=300):
