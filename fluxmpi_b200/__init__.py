@@ -29,7 +29,8 @@ from .runtime import (Init, Initialized, Finalize, local_rank, total_workers, no
                       disable_p2p_support, disable_cudampi_support, p2p_disabled,
                       FluxMPINotInitializedError, host_barrier)
 from .comm import (allreduce_, bcast_, reduce_, Iallreduce, Ibcast, Request, Waitall, barrier,
-                   cpu, gpu, COMM_WORLD, symm_empty, symm_zeros, is_symmetric)
+                   cpu, gpu, COMM_WORLD, symm_empty, symm_zeros, is_symmetric,
+                   register_buffer, deregister_buffer)
 from .tree import fmap, functor
 from . import rules
 from .rules import (AbstractRule, Leaf, setup, update, update_, adjust, Descent, Momentum,

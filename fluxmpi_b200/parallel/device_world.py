@@ -426,19 +426,116 @@ class DeviceWorld(_Base):
                                 [C.byref(c) for c in comms]))
 
     def find_symmetric(self, t: torch.Tensor):
-        """(segment comm refs, byte offset) if ``t`` lives in a registered symmetric segment."""
+        """(comm refs, byte offset, has multicast) if ``t`` lives in a registered symmetric
+        segment or in a user buffer registered with :meth:`register_buffer`."""
         p = t.data_ptr()
         for lo, hi, seg, comms, refs in self._symm_regs:
-            if lo <= p < hi:
-                return refs, p - lo
+            if lo <= p < hi and p + t.numel() * t.element_size() <= hi:
+                return refs, p - lo, bool(comms[0].mc_data)
         return None
 
+    # ------------------------------------------------------------------ user buffers (CUDA IPC)
+    # EXPERIMENTAL (written without GPU time, not yet run): what NCCL calls user-buffer
+    # registration. A tensor from the ordinary allocator is mapped into every peer through the
+    # CUDA-IPC handle of the cudaMalloc block that holds it; collectives on it then use the
+    # in-place peer-to-peer kernels (no staging copies, no multicast) like symm_empty tensors.
+    def register_buffer(self, t: torch.Tensor):
+        """Collective: every rank passes its own contiguous CUDA tensor of the same byte size.
+        Returns a registration object (or None when any rank could not export / map; the
+        tensor then keeps taking the staged path). The mapping is valid while the allocation
+        lives: call :meth:`deregister_buffer` before ``torch.cuda.empty_cache()``."""
+        import struct
+        from .. import runtime
+        if not (self.native and self.world > 1):
+            return None
+        from cuda.bindings import driver as drv, runtime as rt
+        W, r = self.world, self.rank
+        nbytes = t.numel() * t.element_size()
+        ok = t.is_cuda and t.is_contiguous() and t.data_ptr() % 16 == 0 and nbytes > 0 and nbytes % 16 == 0
+        handle, off = bytes(64), 0
+        if ok:
+            err, base, _size = drv.cuMemGetAddressRange(t.data_ptr())
+            ok = int(err) == 0
+            if ok:
+                err, h = rt.cudaIpcGetMemHandle(int(base))
+                ok = int(err) == 0
+                if ok:
+                    handle, off = bytes(h.reserved), t.data_ptr() - int(base)
+        blobs = runtime.host_allgather_bytes(handle + struct.pack("<QQQ", off, nbytes, int(ok)), 88)
+        metas = [(b[:64],) + struct.unpack("<QQQ", b[64:88]) for b in blobs]
+        good = all(m[3] == 1 and m[2] == nbytes for m in metas)
+        ptrs, opened = [0] * W, []
+        if good:
+            for q, (hq, offq, _n, _f) in enumerate(metas):
+                if q == r:
+                    ptrs[q] = t.data_ptr()
+                    continue
+                base_q = self._ipc_open(q, hq)
+                if base_q is None:
+                    good = False
+                    break
+                opened.append((q, hq))
+                ptrs[q] = base_q + offq
+        if not self._all_agree(good):
+            for q, hq in opened:
+                self._ipc_release(q, hq)
+            warnings.warn("[fluxmpi_b200] register_buffer: CUDA-IPC export or mapping failed on some rank; "
+                          "the tensor stays on the staged path")
+            return None
+        comms = [self._mk_comm(ptrs, list(self.base.peer_ptrs), nbytes, ch, r, 0, 0)
+                 for ch in range(_native.NUM_CHANNELS)]
+        entry = (t.data_ptr(), t.data_ptr() + nbytes, ("ipc", opened, t), comms, [C.byref(c) for c in comms])
+        self._symm_regs.append(entry)
+        runtime.host_barrier()
+        return entry
+
+    def deregister_buffer(self, entry) -> None:
+        """Collective. Unmaps the peers' views; later collectives on the tensor are staged."""
+        from .. import runtime
+        if entry is None:
+            return
+        torch.cuda.synchronize(self.device)
+        runtime.host_barrier()                       # nobody is still reading this rank's block
+        if entry in self._symm_regs:
+            self._symm_regs.remove(entry)
+        for q, hq in entry[2][1]:
+            self._ipc_release(q, hq)
+        runtime.host_barrier()
+
+    def _ipc_open(self, q: int, handle: bytes):
+        from cuda.bindings import runtime as rt
+        cache = self.__dict__.setdefault("_ipc_cache", {})
+        hit = cache.get((q, handle))
+        if hit is not None:
+            hit[1] += 1
+            return hit[0]
+        h = rt.cudaIpcMemHandle_t()
+        h.reserved = handle
+        err, ptr = rt.cudaIpcOpenMemHandle(h, rt.cudaIpcMemLazyEnablePeerAccess)
+        if int(err) != 0:
+            return None
+        cache[(q, handle)] = [int(ptr), 1]
+        return int(ptr)
+
+    def _ipc_release(self, q: int, handle: bytes):
+        from cuda.bindings import runtime as rt
+        cache = self.__dict__.get("_ipc_cache", {})
+        hit = cache.get((q, handle))
+        if hit is None:
+            return
+        hit[1] -= 1
+        if hit[1] <= 0:
+            rt.cudaIpcCloseMemHandle(hit[0])
+            del cache[(q, handle)]
+
     def _symm_collective(self, kind: str, t: torch.Tensor, hit, op: int, root: int, channel: int, stream):
-        refs, off = hit
+        refs, off, has_mc = hit
         lib = self._lib
         nbytes = t.numel() * t.element_size()
         st = (torch.cuda.current_stream() if stream is None else stream).cuda_stream
         tl = self.tuner.launch("bcast_symm" if kind == "bcast" else "allreduce_symm", nbytes)
+        if tl and tl[1].algo == _native.ALGO_NVLS and not has_mc:
+            tl = None       # a registered user buffer has no multicast alias: peer-to-peer kernels
         if tl and kind != "bcast" and tl[1].algo == _native.ALGO_NVLS and not (
                 op == _native.SUM and t.dtype in (torch.float32, torch.bfloat16, torch.float16)):
             tl = None       # the switch only adds f32/f16/bf16: other ops/dtypes take the P2P kernel

@@ -54,6 +54,13 @@ def test_engine_without_peer_mappings_over_nccl():
     _run("gpu_engine_fallback.py", 2, env={"FMPI_FORCE_FALLBACK": "1"})
 
 
+@pytest.mark.skipif(__import__("os").environ.get("FMPI_TEST_UNVERIFIED", "0") in ("0", ""),
+                    reason="fm.register_buffer was written without GPU time and has not run yet "
+                           "(set FMPI_TEST_UNVERIFIED=1)")
+def test_registered_user_buffers_run_in_place():
+    _run("gpu_register.py", 2)
+
+
 def test_pretend_nodes_device_tensors_take_nccl():
     """2 pretend nodes x 1 GPU: host world over the TCP mesh, device collectives over NCCL."""
     _run("gpu_collectives.py", 2, args=("quick",), sim_nodes=2)

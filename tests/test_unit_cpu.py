@@ -319,3 +319,74 @@ def test_device_loader_cpu_shuffle_and_remainder():
     again = [int(v) for _, yb in loader for v in yb]
     assert sorted(again) == list(range(23)) and again != seen      # a new permutation every epoch
     assert len(fm.DeviceLoader(data, 5, device="cpu", drop_last=True)) == 4
+
+
+def test_symmetric_lookup_and_dispatch_with_a_mock_library(monkeypatch):
+    """DeviceWorld's symmetric-buffer lookup and kernel dispatch, driven on CPU with a recording
+    stand-in for the CUDA library: offsets, bounds, and the rule that a buffer without a
+    multicast alias (a registered user buffer) never gets the in-switch algorithm."""
+    import ctypes as C
+    from fluxmpi_b200 import _native
+    from fluxmpi_b200.parallel import device_world as DW
+    from fluxmpi_b200.parallel.tuner import Tuner
+
+    class FakeTensor:
+        def __init__(self, ptr, n, dtype=torch.float32):
+            self.ptr, self.n, self.dtype, self.requires_grad = ptr, n, dtype, False
+
+        def data_ptr(self): return self.ptr
+        def numel(self): return self.n
+        def element_size(self): return 4
+        def is_contiguous(self): return True
+
+    class FakeLib:
+        def __init__(self): self.calls = []
+        def fmpi_allreduce_symm(self, ref, off, count, dt, op, lp, st):
+            self.calls.append(("allreduce", off, count, C.cast(lp, C.POINTER(_native.Launch)).contents.algo)); return 0
+        def fmpi_bcast_symm(self, ref, off, nbytes, root, lp, st):
+            self.calls.append(("bcast", off, nbytes, root)); return 0
+        def fmpi_reduce_symm(self, ref, off, count, dt, op, root, lp, st):
+            self.calls.append(("reduce", off, count, root)); return 0
+
+    class FakeStream:
+        cuda_stream = 0
+
+    monkeypatch.setattr(torch.cuda, "current_stream", lambda *a, **k: FakeStream())
+    dw = DW.DeviceWorld(0, 8, 0, "job")
+    dw._lib = FakeLib()
+    dw._lp_auto_obj = _native.Launch(0, 0, _native.ALGO_AUTO)
+    dw._lp_auto = C.byref(dw._lp_auto_obj)
+    dw.tuner = Tuner(8, True)
+
+    def comm(mc):
+        c = _native.DevComm()
+        c.mc_data = mc
+        return c
+
+    with_mc = [comm(0x7000) for _ in range(_native.NUM_CHANNELS)]
+    no_mc = [comm(None) for _ in range(_native.NUM_CHANNELS)]
+    dw._symm_regs.append((0x10000, 0x10000 + (256 << 20), "seg", with_mc, [C.byref(c) for c in with_mc]))
+    dw._symm_regs.append((0x9000_0000, 0x9000_0000 + (64 << 20), ("ipc", [], None), no_mc, [C.byref(c) for c in no_mc]))
+
+    n = (64 << 20) // 4
+    hit = dw._symm_hit(FakeTensor(0x10000 + 4096, n))
+    assert hit is not None and hit[1] == 4096 and hit[2] is True
+    dw._symm_collective("allreduce", FakeTensor(0x10000 + 4096, n), hit, _native.SUM, -1, 0, None)
+    dw._symm_collective("allreduce", FakeTensor(0x10000 + 4096, n), hit, _native.MAX, -1, 0, None)
+    hit2 = dw._symm_hit(FakeTensor(0x9000_0000, n))
+    assert hit2 is not None and hit2[1] == 0 and hit2[2] is False
+    dw._symm_collective("allreduce", FakeTensor(0x9000_0000, n), hit2, _native.SUM, -1, 0, None)
+    dw._symm_collective("bcast", FakeTensor(0x9000_0000, n), hit2, 0, 3, 0, None)
+    dw._symm_collective("reduce", FakeTensor(0x9000_0000, n), hit2, _native.SUM, 2, 0, None)
+    calls = dw._lib.calls
+    assert calls[0][:3] == ("allreduce", 4096, n)
+    tuned_nvls = Tuner(8, True).choice("allreduce_symm", 64 << 20)
+    if tuned_nvls is not None and tuned_nvls[0] == "nvls":
+        assert calls[0][3] == _native.ALGO_NVLS                  # multicast + sum: in-switch
+    assert calls[1][3] != _native.ALGO_NVLS                      # max is not a switch operation
+    assert calls[2][3] != _native.ALGO_NVLS                      # no multicast alias on this buffer
+    assert calls[3] == ("bcast", 0, 64 << 20, 3) and calls[4] == ("reduce", 0, n, 2)
+    # a tensor that sticks out of the registered range, or is misaligned, is not a hit
+    assert dw._symm_hit(FakeTensor(0x9000_0000 + (64 << 20) - 64, 1024)) is None
+    assert dw._symm_hit(FakeTensor(0x10000 + 8, 1024)) is None
+    assert dw.find_symmetric(FakeTensor(0x5000, 16)) is None
