@@ -68,3 +68,11 @@ def test_lost_node_is_an_error_not_a_hang():
     codes, outs = _two_launchers("die_node.py", 2, timeout=120)
     assert codes == [0, 0], "\n".join(outs)[-4000:]
     assert outs[0].count("PEER_LOSS_DETECTED") == 2, outs[0][-4000:]
+
+
+@pytest.mark.parametrize("world,nodes", [(4, 2), (6, 3)])
+def test_randomised_collectives_over_nodes(world, nodes):
+    """tests/spmd/stress.py: a seeded sequence of collectives with sizes around slot / slice /
+    rail boundaries (some with fewer elements than ranks), each checked against an all-gather."""
+    code, outs = run_spmd("stress.py", world, timeout=600, args=("120",), sim_nodes=nodes)
+    assert code == 0 and all(f"RANK_OK {r}" in o for r, o in enumerate(outs)), "\n".join(outs)[-4000:]

@@ -77,3 +77,9 @@ def test_dead_rank_is_detected(spmd):
     SURVEY §5): the launcher kills the job and reports the failing exit code."""
     code, outs = run_spmd("die.py", 3, timeout=120)
     assert code == 3, (code, outs)
+
+
+def test_randomised_collectives(spmd):
+    """tests/spmd/stress.py on one node at the odd world size."""
+    outs = spmd("stress.py", 3, timeout=600, args=("120",))
+    assert all(f"RANK_OK {r}" in o for r, o in enumerate(outs))
