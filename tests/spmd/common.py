@@ -1,5 +1,5 @@
 # SPMD rank script — mirrors /root/reference/test/test_common.jl:1-17 (+ checklist 2-4).
-import io, re, sys, warnings
+import io, re, warnings
 import fluxmpi_b200 as fm
 
 # before Init: rank queries raise, printing shows a timestamp only (src/common.jl:53,65,76-79)

@@ -1,6 +1,5 @@
 """Fused channels-last BatchNorm (+ residual add + ReLU) kernels against PyTorch's own ops
 evaluated in fp32 — forward output, running statistics, and every gradient."""
-import copy
 
 import pytest
 import torch

@@ -20,7 +20,7 @@ if os.environ.get("FMPI_TEST_UNVERIFIED", "0") in ("0", ""):
 import torch.nn.functional as F
 
 from fluxmpi_b200.ops import conv_bn
-from fluxmpi_b200.ops.batchnorm import FusedBatchNormAct, _scratch_for
+from fluxmpi_b200.ops.batchnorm import FusedBatchNormAct
 
 
 def test_library_loads():

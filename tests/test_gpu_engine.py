@@ -14,7 +14,7 @@ if not torch.cuda.is_available():
 import fluxmpi_b200 as fm
 from fluxmpi_b200 import _native
 from fluxmpi_b200 import rules as R
-from fluxmpi_b200.models import resnet_tiny, vit_tiny, gpt2_tiny, quickstart_mlp
+from fluxmpi_b200.models import resnet_tiny, gpt2_tiny, quickstart_mlp
 from fluxmpi_b200.parallel.engine import DataParallelEngine, GraphedStep
 
 

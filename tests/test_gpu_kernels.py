@@ -6,8 +6,6 @@ EmulatedWorld) — the device code (flags, barriers, peer-pointer tables, slice 
 the code that runs across real GPUs. Every numerical check is against a plain PyTorch
 reference of the same op computed in float64 / float32.
 """
-import ctypes as C
-import math
 
 import pytest
 import torch

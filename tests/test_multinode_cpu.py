@@ -4,7 +4,6 @@ it; here the ranks of one machine are split into pretend nodes (``launch --sim-n
 launchers are started the way two real nodes would start them."""
 import functools
 import os
-import socket
 import subprocess
 import sys
 

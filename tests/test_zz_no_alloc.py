@@ -12,7 +12,6 @@ the shared scratch — and it must refuse inputs beyond its documented limit.
 
 Works in a fresh process (no Init, no other kernels run first) and after the whole suite.
 """
-import ctypes as C
 
 import pytest
 import torch
