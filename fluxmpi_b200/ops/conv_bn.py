@@ -86,35 +86,54 @@ def eligible(x: torch.Tensor, conv: torch.nn.Conv2d, bn: torch.nn.Module, residu
     return gemm_lib() is not None
 
 
+# The three native steps, each behind a function of tensors so that a CPU test can stand in
+# plain-PyTorch versions and check the autograd plumbing around them (tests/test_unit_cpu.py).
+def _k_gemm_stats(x, w2, y, scratch, M, N, K):
+    """y = x w2^T; column sums of the accumulators into scratch[0:N], of their squares into [N:2N]."""
+    gl = gemm_lib()
+    ws = _workspace_for(x.device, gl.fmpi_conv1x1_bnstats_workspace(M, N, K))
+    if gl.fmpi_conv1x1_bnstats(x.data_ptr(), w2.data_ptr(), y.data_ptr(), scratch.data_ptr(),
+                               scratch.data_ptr() + 4 * N, M, N, K, ws.data_ptr(), ws.numel(), B._stream()):
+        raise _native.NativeError("conv1x1_bnstats: " + gl.fmpi_gemm_last_error().decode(errors="replace"))
+
+
+def _k_bn_fwd(y, residual, z, M, N, g, b, running_mean, running_var, momentum, eps, relu, mean, invstd, scratch):
+    ptr = lambda t: t.data_ptr() if t is not None else None
+    _native.cuda_check(_native.cuda().fmpi_bn_forward_presummed(
+        y.data_ptr(), ptr(residual), z.data_ptr(), M, N, B._DT[y.dtype], ptr(g), ptr(b), ptr(running_mean),
+        ptr(running_var), float(momentum), float(eps), int(relu), mean.data_ptr(), invstd.data_ptr(),
+        scratch.data_ptr(), B._stream()), "bn_forward_presummed")
+
+
+def _k_bn_bwd(dz, z, y, dy, dres, M, N, g, mean, invstd, dgamma, dbeta, relu):
+    ptr = lambda t: t.data_ptr() if t is not None else None
+    _native.cuda_check(_native.cuda().fmpi_bn_backward(
+        dz.data_ptr(), ptr(z), y.data_ptr(), dy.data_ptr(), ptr(dres), M, N, B._DT[y.dtype], ptr(g),
+        mean.data_ptr(), invstd.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), int(relu),
+        B._scratch_for(y.device, N).data_ptr(), B._stream()), "bn_backward")
+
+
+def _scratch(device, N):
+    return B._scratch_for(device, N)
+
+
 class _ConvBNActFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, residual, gamma, beta, running_mean, running_var, momentum, eps, relu):
-        lib, gl = _native.cuda(), gemm_lib()
         Bn, K, H, W = x.shape
         N = weight.shape[0]
         M = Bn * H * W
         dev = x.device
         w2 = weight.detach().reshape(N, K).to(x.dtype).contiguous()
         y = torch.empty((Bn, N, H, W), dtype=x.dtype, device=dev, memory_format=torch.channels_last)
-        scratch = B._scratch_for(dev, N)                       # sums land in its first 2*N floats
-        ws_bytes = gl.fmpi_conv1x1_bnstats_workspace(M, N, K)
-        ws = _workspace_for(dev, ws_bytes)
-        st = B._stream()
-        if gl.fmpi_conv1x1_bnstats(x.data_ptr(), w2.data_ptr(), y.data_ptr(), scratch.data_ptr(),
-                                   scratch.data_ptr() + 4 * N, M, N, K, ws.data_ptr(), ws.numel(), st):
-            raise _native.NativeError("conv1x1_bnstats: " + gl.fmpi_gemm_last_error().decode(errors="replace"))
+        scratch = _scratch(dev, N)                             # sums land in its first 2*N floats
+        _k_gemm_stats(x, w2, y, scratch, M, N, K)
         z = torch.empty_like(y)
         mean = torch.empty(N, dtype=torch.float32, device=dev)
         invstd = torch.empty(N, dtype=torch.float32, device=dev)
         g = gamma.detach().float() if gamma is not None else None
         b = beta.detach().float() if beta is not None else None
-        _native.cuda_check(lib.fmpi_bn_forward_presummed(
-            y.data_ptr(), residual.data_ptr() if residual is not None else None, z.data_ptr(), M, N,
-            B._DT[x.dtype], g.data_ptr() if g is not None else None, b.data_ptr() if b is not None else None,
-            running_mean.data_ptr() if running_mean is not None else None,
-            running_var.data_ptr() if running_var is not None else None,
-            float(momentum), float(eps), int(relu), mean.data_ptr(), invstd.data_ptr(),
-            scratch.data_ptr(), st), "bn_forward_presummed")
+        _k_bn_fwd(y, residual, z, M, N, g, b, running_mean, running_var, momentum, eps, relu, mean, invstd, scratch)
         _native.count_launch(3)
         ctx.relu, ctx.has_res = bool(relu), residual is not None
         ctx.affine = (gamma is not None, beta is not None)
@@ -125,7 +144,6 @@ class _ConvBNActFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dz):
-        lib = _native.cuda()
         x, w2, y, z, g, mean, invstd = ctx.saved_tensors
         Bn, K, H, W = x.shape
         N = w2.shape[0]
@@ -136,15 +154,10 @@ class _ConvBNActFn(torch.autograd.Function):
         dres = torch.empty_like(y) if (ctx.has_res and ctx.relu) else None
         dgamma = torch.empty(N, dtype=torch.float32, device=x.device)
         dbeta = torch.empty(N, dtype=torch.float32, device=x.device)
-        _native.cuda_check(lib.fmpi_bn_backward(
-            dz.data_ptr(), z.data_ptr() if z is not None else None, y.data_ptr(), dy.data_ptr(),
-            dres.data_ptr() if dres is not None else None, M, N, B._DT[x.dtype],
-            g.data_ptr() if g is not None else None, mean.data_ptr(), invstd.data_ptr(),
-            dgamma.data_ptr(), dbeta.data_ptr(), int(ctx.relu), B._scratch_for(x.device, N).data_ptr(),
-            B._stream()), "bn_backward")
+        _k_bn_bwd(dz, z, y, dy, dres, M, N, g, mean, invstd, dgamma, dbeta, ctx.relu)
         _native.count_launch(3)
         if ctx.has_res and not ctx.relu:
-            dres = dz
+            dres = dz                                          # d(bn + r)/dr = 1: the same gradient
         dy2 = dy.permute(0, 2, 3, 1).reshape(M, N)             # views of NHWC memory
         x2 = x.permute(0, 2, 3, 1).reshape(M, K)
         dx = dw = None

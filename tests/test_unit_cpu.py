@@ -390,3 +390,85 @@ def test_symmetric_lookup_and_dispatch_with_a_mock_library(monkeypatch):
     assert dw._symm_hit(FakeTensor(0x9000_0000 + (64 << 20) - 64, 1024)) is None
     assert dw._symm_hit(FakeTensor(0x10000 + 8, 1024)) is None
     assert dw.find_symmetric(FakeTensor(0x5000, 16)) is None
+
+
+@pytest.mark.parametrize("relu,res", [(True, False), (True, True), (False, True), (False, False)])
+def test_conv_bn_autograd_plumbing_with_stand_in_kernels(monkeypatch, relu, res):
+    """ops/conv_bn.py on CPU: its three native steps are replaced by plain-PyTorch versions of
+    what the kernels compute, so the autograd function around them — NHWC views, saved tensors,
+    dX = dY W, dW = dY^T X, the residual / ReLU gradient routing, running statistics — is
+    checked against F.conv2d + F.batch_norm without a GPU."""
+    from fluxmpi_b200.ops import conv_bn
+    from fluxmpi_b200.ops.batchnorm import FusedBatchNormAct
+
+    def nhwc(t):
+        return t.permute(0, 2, 3, 1).reshape(-1, t.shape[1])          # a view of channels_last memory
+
+    def gemm_stats(x, w2, y, scratch, M, N, K):
+        acc = nhwc(x).float() @ w2.float().t()
+        nhwc(y).copy_(acc.to(y.dtype))
+        scratch[:N] = acc.sum(0)
+        scratch[N:2 * N] = (acc * acc).sum(0)
+
+    def bn_fwd(y, residual, z, M, N, g, b, rm, rv, momentum, eps, relu_, mean, invstd, scratch):
+        m = scratch[:N].double() / M
+        var = (scratch[N:2 * N].double() / M - m * m).clamp_min(0)
+        mean.copy_(m)
+        invstd.copy_(1.0 / torch.sqrt(var + eps))
+        scale = (g if g is not None else 1.0) * invstd
+        shift = (b if b is not None else 0.0) - mean * scale
+        out = nhwc(y).float() * scale + shift
+        if residual is not None:
+            out = out + nhwc(residual).float()
+        nhwc(z).copy_((out.relu() if relu_ else out).to(z.dtype))
+        if rm is not None:
+            rm.mul_(1 - momentum).add_(momentum * mean)
+            rv.mul_(1 - momentum).add_(momentum * (var * M / (M - 1)).float())
+
+    def bn_bwd(dz, z, y, dy, dres, M, N, g, mean, invstd, dgamma, dbeta, relu_):
+        gz = nhwc(dz).float()
+        if relu_:
+            gz = gz * (nhwc(z).float() > 0)
+        if dres is not None:
+            nhwc(dres).copy_(gz.to(dres.dtype))
+        xhat = (nhwc(y).float() - mean) * invstd
+        dbeta.copy_(gz.sum(0))
+        dgamma.copy_((gz * xhat).sum(0))
+        scale = (g if g is not None else 1.0) * invstd
+        nhwc(dy).copy_((scale * (gz - dbeta / M - xhat * dgamma / M)).to(dy.dtype))
+
+    monkeypatch.setattr(conv_bn, "_k_gemm_stats", gemm_stats)
+    monkeypatch.setattr(conv_bn, "_k_bn_fwd", bn_fwd)
+    monkeypatch.setattr(conv_bn, "_k_bn_bwd", bn_bwd)
+    monkeypatch.setattr(conv_bn, "_scratch", lambda dev, N: torch.zeros(2 * N + 64))
+    monkeypatch.setattr(conv_bn, "eligible", lambda *a: True)
+
+    torch.manual_seed(3)
+    Bn, K, H, W, N = 3, 16, 5, 4, 24
+    conv = torch.nn.Conv2d(K, N, 1, bias=False).to(memory_format=torch.channels_last)
+    bn, ref_bn = FusedBatchNormAct(N, relu=relu), torch.nn.BatchNorm2d(N)
+    with torch.no_grad():
+        bn.weight.uniform_(0.5, 1.5)
+        bn.bias.uniform_(-0.5, 0.5)
+    ref_bn.load_state_dict(bn.state_dict())
+    x = torch.randn(Bn, K, H, W).contiguous(memory_format=torch.channels_last)
+    r = torch.randn(Bn, N, H, W).contiguous(memory_format=torch.channels_last) if res else None
+    xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    ra = r.clone().requires_grad_(True) if res else None
+    rb = r.clone().requires_grad_(True) if res else None
+    up = torch.randn(Bn, N, H, W)
+
+    z = conv_bn.conv1x1_bn_act(xa, conv, bn, ra)
+    got = torch.autograd.grad(z, [xa, conv.weight, bn.weight, bn.bias] + ([ra] if res else []), up)
+    t = ref_bn(torch.nn.functional.conv2d(xb, conv.weight))
+    t = t + rb if res else t
+    t = torch.relu(t) if relu else t
+    want = torch.autograd.grad(t, [xb, conv.weight, ref_bn.weight, ref_bn.bias] + ([rb] if res else []), up)
+
+    assert z.shape == t.shape and z.is_contiguous(memory_format=torch.channels_last)
+    assert torch.allclose(z, t, rtol=1e-4, atol=1e-5)
+    for a, b in zip(got, want):
+        assert a.shape == b.shape and torch.allclose(a, b, rtol=1e-3, atol=1e-4), float((a - b).abs().max())
+    assert torch.allclose(bn.running_mean, ref_bn.running_mean, atol=1e-6)
+    assert torch.allclose(bn.running_var, ref_bn.running_var, atol=1e-6)
+    assert int(bn.num_batches_tracked) == 1
