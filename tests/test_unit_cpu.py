@@ -472,3 +472,71 @@ def test_conv_bn_autograd_plumbing_with_stand_in_kernels(monkeypatch, relu, res)
     assert torch.allclose(bn.running_mean, ref_bn.running_mean, atol=1e-6)
     assert torch.allclose(bn.running_var, ref_bn.running_var, atol=1e-6)
     assert int(bn.num_batches_tracked) == 1
+
+
+def test_register_buffer_bookkeeping_with_mock_cuda(monkeypatch):
+    """DeviceWorld.register_buffer / deregister_buffer with the CUDA driver, the IPC calls and
+    the host world replaced by recorders: handle exchange, per-peer pointers (base + that peer's
+    offset), the open-handle cache with reference counts, and the lookup that follows."""
+    import struct
+    import sys
+    import types
+    from fluxmpi_b200 import _native, runtime
+    from fluxmpi_b200.parallel import device_world as DW
+
+    opened, closed = [], []
+
+    class H:
+        reserved = b""
+
+    drv = types.SimpleNamespace(cuMemGetAddressRange=lambda p: (0, 0x7000_0000, 1 << 30))
+    rt = types.SimpleNamespace(
+        cudaIpcGetMemHandle=lambda base: (0, types.SimpleNamespace(reserved=b"L" * 64)),
+        cudaIpcMemHandle_t=H, cudaIpcMemLazyEnablePeerAccess=1,
+        cudaIpcOpenMemHandle=lambda h, flags: (opened.append(bytes(h.reserved)) or 0, 0x9000_0000),
+        cudaIpcCloseMemHandle=lambda p: (closed.append(p) or 0,))
+    pkg = types.ModuleType("cuda.bindings")
+    pkg.driver, pkg.runtime = drv, rt
+    monkeypatch.setitem(sys.modules, "cuda.bindings", pkg)
+    monkeypatch.setitem(sys.modules, "cuda.bindings.driver", drv)
+    monkeypatch.setitem(sys.modules, "cuda.bindings.runtime", rt)
+
+    class FakeTensor:
+        is_cuda, requires_grad, dtype = True, False, torch.float32
+
+        def __init__(self, ptr, n): self.ptr, self.n = ptr, n
+        def data_ptr(self): return self.ptr
+        def numel(self): return self.n
+        def element_size(self): return 4
+        def is_contiguous(self): return True
+
+    dw = DW.DeviceWorld(0, 2, 0, "job")
+    dw.native = True
+    dw.base = DW.Segment(None, 0x1000, 1 << 20, [0x1000, 0x2000], 0, "vmm")
+    peer = b"P" * 64 + struct.pack("<QQQ", 4096, 1 << 20, 1)          # rank 1: offset 4096 in its block
+    monkeypatch.setattr(runtime, "host_allgather_bytes",
+                        lambda blob, size=None: [blob, peer] if len(blob) == 88 else [blob, blob])
+    monkeypatch.setattr(runtime, "host_barrier", lambda: None)
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: None)
+
+    t = FakeTensor(0x7000_0000 + 256, (1 << 20) // 4)
+    reg = dw.register_buffer(t)
+    assert reg is not None and opened == [b"P" * 64]
+    comm = reg[3][0]
+    assert comm.world == 2 and comm.rank == 0 and comm.data[0] == t.data_ptr()
+    assert comm.data[1] == 0x9000_0000 + 4096 and comm.sig[1] == 0x2000 and not comm.mc_data
+    hit = dw._symm_hit(FakeTensor(t.data_ptr() + 1024, 256))
+    assert hit is not None and hit[1] == 1024 and hit[2] is False
+    reg2 = dw.register_buffer(FakeTensor(0x7000_0000 + 256, (1 << 20) // 4))   # same peer block: cached
+    assert reg2 is not None and len(opened) == 1
+    dw.deregister_buffer(reg)
+    assert closed == [] and dw._symm_hit(t) is not None                         # still held by reg2
+    dw.deregister_buffer(reg2)
+    assert closed == [0x9000_0000] and dw._symm_hit(t) is None
+    # sizes that differ between ranks, or an unaligned tensor, are refused on every rank
+    monkeypatch.setattr(runtime, "host_allgather_bytes",
+                        lambda blob, size=None: [blob, b"P" * 64 + struct.pack("<QQQ", 0, 512, 1)]
+                        if len(blob) == 88 else [blob, blob])
+    with pytest.warns(UserWarning):
+        assert dw.register_buffer(t) is None
+    assert len(opened) == 1
