@@ -75,3 +75,14 @@ def test_randomised_collectives_over_nodes(world, nodes):
     rail boundaries (some with fewer elements than ranks), each checked against an all-gather."""
     code, outs = run_spmd("stress.py", world, timeout=600, args=("120",), sim_nodes=nodes)
     assert code == 0 and all(f"RANK_OK {r}" in o for r, o in enumerate(outs)), "\n".join(outs)[-4000:]
+
+
+def test_pipelined_all_reduce_over_nodes():
+    """Large all-reduces of a multi-node job overlap their network step with the shared-memory
+    steps of the neighbouring chunks (helper thread, two result slots). Forced here for every
+    message of the randomised test and of the tree / dtype matrix (tiny slots = many chunks)."""
+    env = {"FMPI_HOST_PIPELINE_MIN_BYTES": "1"}
+    code, outs = run_spmd("stress.py", 4, timeout=600, args=("120",), sim_nodes=2, env=env)
+    assert code == 0 and all(f"RANK_OK {r}" in o for r, o in enumerate(outs)), "\n".join(outs)[-4000:]
+    code, outs = run_spmd("mpi_extensions.py", 6, timeout=600, sim_nodes=3, env=env)
+    assert code == 0 and all(f"RANK_OK {r}" in o for r, o in enumerate(outs)), "\n".join(outs)[-4000:]
