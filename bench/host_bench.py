@@ -58,6 +58,10 @@ def sweep(dist, max_mb):
         warm = max(3, iters // 10)
         row = {"bytes": n * 4}
         row["allreduce_us"] = round(timed(lambda: fm.allreduce_(x, "sum"), iters, warm), 2)
+        if n * 4 >= (1 << 16):          # the same on a tensor in symmetric host memory (fm.shm_empty)
+            sx = fm.shm_empty((n,), torch.float32)
+            sx.fill_(1)
+            row["allreduce_symm_us"] = round(timed(lambda: fm.allreduce_(sx, "sum"), iters, warm), 2)
         x.fill_(1)
         row["bcast_us"] = round(timed(lambda: fm.bcast_(x, 0), iters, warm), 2)
         if dist is not None:

@@ -96,6 +96,14 @@ def host():
         lib.fmpi_net_allgather.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
         lib.fmpi_host_allreduce_many.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                                  C.c_int, C.c_int]
+        lib.fmpi_host_symm_alloc.argtypes = [C.c_void_p, C.c_size_t, C.POINTER(C.c_void_p)]
+        lib.fmpi_host_symm_ptr.argtypes = [C.c_void_p]
+        lib.fmpi_host_symm_ptr.restype = C.c_void_p
+        lib.fmpi_host_symm_bytes.argtypes = [C.c_void_p]
+        lib.fmpi_host_symm_bytes.restype = C.c_size_t
+        lib.fmpi_host_symm_free.argtypes = [C.c_void_p, C.c_void_p]
+        lib.fmpi_host_allreduce_symm.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,
+                                                 C.c_int, C.c_int]
         lib.fmpi_host_multi_tensor_step.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                                     C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                                     C.c_void_p, C.c_int64]

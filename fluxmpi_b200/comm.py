@@ -124,12 +124,60 @@ def _host_view(t: torch.Tensor):
     return t.contiguous(), True
 
 
+def shm_empty(shape, dtype=torch.float32) -> torch.Tensor:
+    """Collective: a CPU tensor in symmetric host memory (every rank must call it with the same
+    shape, in the same order) — the host twin of :func:`symm_empty`. ``allreduce_`` on it (or on
+    a contiguous slice) runs in place through the peers' mappings, with no staging copies
+    (csrc/host_backend.cpp ``fmpi_host_allreduce_symm``). The memory lives until ``Finalize``;
+    with one worker this is a plain ``torch.empty``."""
+    if not runtime.Initialized():
+        raise runtime.FluxMPINotInitializedError()
+    S = runtime.state()
+    numel = 1
+    for d in (shape if isinstance(shape, (tuple, list, torch.Size)) else (shape,)):
+        numel *= int(d)
+    if S.world == 1 or S.host_comm is None or numel == 0:
+        return torch.empty(shape, dtype=dtype)
+    nbytes = numel * torch.empty((), dtype=dtype).element_size()
+    lib = _native.host()
+
+    def alloc():
+        h = C.c_void_p()
+        _native.host_check(lib.fmpi_host_symm_alloc(S.host_comm, nbytes, C.byref(h)), "host_symm_alloc")
+        return h
+
+    h = runtime.host_run(alloc)
+    ptr = lib.fmpi_host_symm_ptr(h)
+    buf = (C.c_char * nbytes).from_address(ptr)
+    S.host_symm.append((ptr, ptr + nbytes, h, buf))
+    return torch.frombuffer(buf, dtype=dtype, count=numel).view(shape)
+
+
+def _host_symm_hit(t: torch.Tensor):
+    """(segment handle, byte offset) when ``t`` lies inside a block from :func:`shm_empty`."""
+    regs = runtime.state().host_symm
+    if not regs or not t.is_contiguous():
+        return None
+    p, n = t.data_ptr(), t.numel() * t.element_size()
+    for lo, hi, h, _ in regs:
+        if lo <= p and p + n <= hi:
+            return h, p - lo
+    return None
+
+
 def _host_allreduce_now(send: torch.Tensor, recv: torch.Tensor, op: int):
     S = runtime.state()
     if S.world == 1:
         if recv.data_ptr() != send.data_ptr():
             recv.copy_(send)
         return
+    if send.data_ptr() == recv.data_ptr() and send.dtype != torch.bool:
+        hit = _host_symm_hit(recv)
+        if hit is not None:
+            _native.host_check(
+                _native.host().fmpi_host_allreduce_symm(S.host_comm, hit[0], hit[1], recv.numel(),
+                                                        dtype_code(recv.dtype), op), "allreduce (symmetric)")
+            return
     s, _ = _host_view(send)
     r, back = _host_view(recv)
     _native.host_check(

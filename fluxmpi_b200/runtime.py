@@ -64,6 +64,7 @@ class _State:
     topology: dict = field(default_factory=dict)
     timeout_s: float = 300.0
     slot_bytes: int = 8 << 20                 # staging slot of the host world
+    host_symm: list = field(default_factory=list)   # (lo, hi, handle, buffer) of comm.shm_empty blocks
     lock: threading.Lock = field(default_factory=threading.Lock)
     host_exec: threading.Lock = field(default_factory=threading.Lock)   # one host collective at a time
     host_count: threading.Lock = field(default_factory=threading.Lock)  # guards host_pending
@@ -232,6 +233,9 @@ def Finalize() -> None:
         if _S.host_pool is not None:
             _S.host_pool.shutdown(wait=True)
             _S.host_pool = None
+        for _lo, _hi, handle, _buf in _S.host_symm:      # unmap without a barrier: peers may be gone
+            _native.host().fmpi_host_symm_free(None, handle)
+        _S.host_symm = []
         if _S.host_comm is not None:
             _native.host().fmpi_host_finalize(_S.host_comm)
             _S.host_comm = None

@@ -85,6 +85,17 @@ int fmpi_host_allreduce(fmpi_host_comm* c, const void* send, void* recv, size_t 
  * the barriers of one message, no flattening copy. */
 int fmpi_host_allreduce_many(fmpi_host_comm* c, int n, void* const* bufs, const uint64_t* counts,
                              int dtype, int op);
+/* Symmetric host memory (the CPU twin of fmpi_symm_*): every rank allocates nbytes in shared
+ * memory and maps its node peers' blocks; an all-reduce on a range of it runs in place, without
+ * staging copies. alloc / free are collective and must be issued in the same order everywhere.
+ * Over several nodes, and for 16-bit floats, the all-reduce takes the slot path on the block. */
+typedef struct fmpi_host_symm fmpi_host_symm;
+int fmpi_host_symm_alloc(fmpi_host_comm* c, size_t nbytes, fmpi_host_symm** out);
+void* fmpi_host_symm_ptr(fmpi_host_symm* s);
+size_t fmpi_host_symm_bytes(fmpi_host_symm* s);
+int fmpi_host_symm_free(fmpi_host_comm* c, fmpi_host_symm* s);
+int fmpi_host_allreduce_symm(fmpi_host_comm* c, fmpi_host_symm* s, size_t offset_bytes, size_t count,
+                             int dtype, int op);
 int fmpi_host_bcast(fmpi_host_comm* c, void* buf, size_t nbytes, int root);
 /* Only root's recv is written; non-root buffers are left untouched
  * (test/test_mpi_extensions.jl:56-60). */

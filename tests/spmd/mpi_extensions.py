@@ -95,6 +95,28 @@ try:
 except ValueError:
     pass
 
+# symmetric host memory: in-place all-reduce through the peers' mappings, bit for bit equal to
+# the slot path, on whole tensors, slices at odd offsets, every native dtype and op
+for dt in (torch.float32, torch.float64, torch.int32, torch.int64, torch.uint8, torch.bfloat16):
+    n = 70001
+    sym = fm.shm_empty((n,), dt)
+    assert sym.shape == (n,) and sym.dtype == dt and sym.is_contiguous()
+    for op in ("sum", "max", "min"):
+        src = (torch.rand(n, generator=gen, dtype=torch.float64) * 3 + 1).to(dt)
+        ref = fm.allreduce_(src.clone(), op)
+        sym.copy_(src)
+        out = fm.allreduce_(sym, op)
+        assert out is sym and torch.equal(sym, ref), (dt, op)
+        sym.copy_(src)
+        part = sym[1234:1234 + 4097]                        # a view inside the block
+        fm.allreduce_(part, op)
+        assert torch.equal(part, ref[1234:1234 + 4097]) and torch.equal(sym[:1234], src[:1234]), (dt, op)
+        assert torch.equal(sym[1234 + 4097:], src[1234 + 4097:]), (dt, op)
+two = fm.shm_empty((3, 5), torch.float32)                   # a second block, different shape
+two.fill_(float(r + 1))
+fm.allreduce_(two, "sum")
+assert torch.equal(two, torch.full((3, 5), w * (w + 1) / 2))
+
 # a gradient tree as ONE message: leaves of odd sizes that straddle the 64 KB slots, compared
 # bit for bit with one all-reduce per leaf
 for dt in (torch.float32, torch.float64):
