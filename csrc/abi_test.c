@@ -84,6 +84,20 @@ static int run_rank(const char* name, int rank, int world, int nodes, int port) 
     if (tb[i] != tri * (i % 7)) { fprintf(stderr, "rank %d: allreduce_many wrong at %d\n", rank, i); return 8; }
   if (ta[NA - 1] != tri || tc[0] != tri) return 9;
 
+  /* symmetric host memory: all-reduce in place on a range that starts inside the block */
+  fmpi_host_symm* seg = NULL;
+  CHECK(fmpi_host_symm_alloc(c, sizeof(float) * 100000, &seg));
+  float* sm = (float*)fmpi_host_symm_ptr(seg);
+  if (!sm || fmpi_host_symm_bytes(seg) < sizeof(float) * 100000) return 12;
+  for (int i = 0; i < 100000; ++i) sm[i] = (float)(rank + 1);
+  CHECK(fmpi_host_allreduce_symm(c, seg, sizeof(float) * 7, 90001, FMPI_F32, FMPI_SUM));
+  for (int i = 0; i < 100000; ++i) {
+    const float want = (i >= 7 && i < 7 + 90001) ? (float)tri : (float)(rank + 1);
+    if (sm[i] != want) { fprintf(stderr, "rank %d: allreduce_symm wrong at %d\n", rank, i); return 13; }
+  }
+  if (fmpi_host_allreduce_symm(c, seg, 0, 1u << 30, FMPI_F32, FMPI_SUM) == 0) return 14; /* out of range */
+  CHECK(fmpi_host_symm_free(c, seg));
+
   /* the rule loop: x -= eta * g over two leaves */
   float p1[3] = {1, 1, 1}, p2[1] = {4}, g1[3] = {2, 2, 2}, g2[1] = {8};
   void* ps[2] = {p1, p2};
