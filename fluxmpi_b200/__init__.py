@@ -51,4 +51,7 @@ def __getattr__(name):
     if name == "DataParallelEngine":
         from .parallel.engine import DataParallelEngine
         return DataParallelEngine
+    if name in ("HostDataParallelEngine", "make_engine"):
+        from .parallel import host_engine
+        return getattr(host_engine, name)
     raise AttributeError(name)

@@ -86,3 +86,8 @@ def test_pipelined_all_reduce_over_nodes():
     assert code == 0 and all(f"RANK_OK {r}" in o for r, o in enumerate(outs)), "\n".join(outs)[-4000:]
     code, outs = run_spmd("mpi_extensions.py", 6, timeout=600, sim_nodes=3, env=env)
     assert code == 0 and all(f"RANK_OK {r}" in o for r, o in enumerate(outs)), "\n".join(outs)[-4000:]
+
+
+def test_host_engine_over_nodes():
+    code, outs = run_spmd("host_engine.py", 4, timeout=300, sim_nodes=2)
+    assert code == 0 and all(f"RANK_OK {r}" in o for r, o in enumerate(outs)), "\n".join(outs)[-4000:]

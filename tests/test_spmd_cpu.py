@@ -83,3 +83,9 @@ def test_randomised_collectives(spmd):
     """tests/spmd/stress.py on one node at the odd world size."""
     outs = spmd("stress.py", 3, timeout=600, args=("120",))
     assert all(f"RANK_OK {r}" in o for r, o in enumerate(outs))
+
+
+def test_host_engine_matches_torch_optim(spmd):
+    """HostDataParallelEngine: flat vectors, gradient in symmetric host memory, native rule loop."""
+    outs = spmd("host_engine.py", 3, timeout=300)
+    assert all(f"RANK_OK {r}" in o for r, o in enumerate(outs))
