@@ -89,3 +89,21 @@ def test_host_engine_matches_torch_optim(spmd):
     """HostDataParallelEngine: flat vectors, gradient in symmetric host memory, native rule loop."""
     outs = spmd("host_engine.py", 3, timeout=300)
     assert all(f"RANK_OK {r}" in o for r, o in enumerate(outs))
+
+
+def test_examples_run_on_cpu(tmp_path):
+    """examples/ stay runnable: the any-device engine example (with checkpoint + resume) and the
+    functional quick start, two ranks each."""
+    import os
+    from conftest import ROOT
+    from fluxmpi_b200.launch import launch
+    env = {"PYTHONPATH": str(ROOT) + os.pathsep + os.environ.get("PYTHONPATH", ""), "FMPI_TIMEOUT_S": "60",
+           "OMP_NUM_THREADS": "1"}
+    ck = str(tmp_path / "ck.pt")
+    ex = str(ROOT / "examples" / "engine_any_device.py")
+    code, outs = launch(2, [ex, "--epochs", "100", "--checkpoint", ck], timeout=240, env_extra=env, capture=True)
+    assert code == 0 and "HostDataParallelEngine" in outs[0], outs[0][-3000:]
+    code, outs = launch(2, [ex, "--epochs", "150", "--checkpoint", ck], timeout=240, env_extra=env, capture=True)
+    assert code == 0 and "resumed at epoch 100" in outs[0], outs[0][-3000:]
+    code, outs = launch(2, [str(ROOT / "examples" / "quickstart_mlp.py")], timeout=240, env_extra=env, capture=True)
+    assert code == 0, outs[0][-3000:]
