@@ -83,6 +83,27 @@ def quickstart(mode, epochs, dist):
     r, w = fm.local_rank(), fm.total_workers()
     torch.manual_seed(r)
     model = quickstart_mlp()
+    if mode == "engine":        # HostDataParallelEngine: flat vectors, symmetric host gradient buffer
+        eng = fm.make_engine(model, fm.DistributedOptimizer(R.Adam(0.001)))
+        x = torch.rand(16, 1)
+        y = x ** 2
+
+        def estep():
+            l = ((model(x) - y) ** 2).sum() / w
+            l.backward()
+            eng.step()
+            return l
+
+        for _ in range(5):
+            estep()
+        fm.barrier()
+        t0 = time.perf_counter()
+        for _ in range(epochs):
+            l = estep()
+        fm.barrier()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64)
+        fm.allreduce_(dt, "max")
+        return epochs / float(dt), float(l.detach())
     ps = {k: v.detach().clone().requires_grad_(True) for k, v in model.named_parameters()}
     ps = fm.synchronize(ps, root_rank=0)
     x = torch.rand(16, 1)
@@ -136,7 +157,7 @@ def main():
         dist.init_process_group("gloo", rank=r, world_size=w)
     rows = sweep(dist, a.max_mb)
     qs = {}
-    for mode in ("ours", "ref_shape") + (("ref_shape_gloo",) if dist is not None else ()):
+    for mode in ("ours", "engine", "ref_shape") + (("ref_shape_gloo",) if dist is not None else ()):
         eps, last = quickstart(mode, a.epochs, dist)
         qs[mode] = {"epochs_per_s": round(eps, 1), "last_local_loss": last}
         if r == 0:
