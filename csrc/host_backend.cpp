@@ -853,6 +853,22 @@ int fmpi_host_allreduce_symm(fmpi_host_comm* c, fmpi_host_symm* s, size_t offset
   return c->barrier();                                   // nobody is still reading my block
 }
 
+// Broadcast on symmetric host memory: everybody copies the range straight out of the root's
+// block (one pass, no slots). Over several nodes the slot path carries it.
+int fmpi_host_bcast_symm(fmpi_host_comm* c, fmpi_host_symm* s, size_t offset_bytes, size_t nbytes, int root) {
+  if (!c || !s) return fail("null communicator or segment");
+  if (root < 0 || root >= c->nnodes * c->world) return fail("bad root %d", root);
+  if (offset_bytes + nbytes > s->bytes)
+    return fail("range [%zu, +%zu) is outside the %zu-byte symmetric block", offset_bytes, nbytes, s->bytes);
+  if (s->world != c->world) return fail("segment belongs to another world");
+  uint8_t* mine = s->peer[size_t(c->rank)] + offset_bytes;
+  if (c->nnodes > 1) return fmpi_host_bcast(c, mine, nbytes, root);
+  if (c->world == 1 || nbytes == 0) return 0;
+  if (c->barrier()) return 1;                                   // the root's data is complete
+  if (c->rank != root) memcpy(mine, s->peer[size_t(root)] + offset_bytes, nbytes);
+  return c->barrier();                                          // the root may overwrite it again
+}
+
 int fmpi_host_bcast(fmpi_host_comm* c, void* buf, size_t nbytes, int root) {
   if (!c) return fail("null communicator");
   if (root < 0 || root >= c->nnodes * c->world) return fail("bad root %d", root);

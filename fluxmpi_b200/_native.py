@@ -104,6 +104,7 @@ def host():
         lib.fmpi_host_symm_free.argtypes = [C.c_void_p, C.c_void_p]
         lib.fmpi_host_allreduce_symm.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t,
                                                  C.c_int, C.c_int]
+        lib.fmpi_host_bcast_symm.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int]
         lib.fmpi_host_multi_tensor_step.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
                                                     C.c_void_p, C.c_void_p, C.c_int, C.c_int,
                                                     C.c_void_p, C.c_int64]

@@ -205,6 +205,12 @@ def _host_bcast_now(buf: torch.Tensor, root: int):
     S = runtime.state()
     if S.world == 1:
         return
+    hit = _host_symm_hit(buf)
+    if hit is not None:            # symmetric host memory: copied straight out of the root's block
+        _native.host_check(
+            _native.host().fmpi_host_bcast_symm(S.host_comm, hit[0], hit[1], buf.numel() * buf.element_size(),
+                                                root), "bcast (symmetric)")
+        return
     b, back = _host_view(buf)
     _native.host_check(
         _native.host().fmpi_host_bcast(S.host_comm, b.data_ptr(), b.numel() * b.element_size(),

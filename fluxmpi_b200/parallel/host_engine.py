@@ -57,8 +57,11 @@ class HostDataParallelEngine:
             self.offsets.append(cur)
             cur += (p.numel() + _ELEM_ALIGN - 1) // _ELEM_ALIGN * _ELEM_ALIGN
         self.numel = cur
-        self.P = torch.zeros(cur, dtype=self.dtype)
-        self.G = comm.shm_empty((cur,), self.dtype)          # collective; plain memory at one worker
+        # both flat vectors in symmetric host memory (collective; plain memory at one worker):
+        # the gradient all-reduce and the parameter broadcast then run in place
+        self.P = comm.shm_empty((cur,), self.dtype)
+        self.P.zero_()
+        self.G = comm.shm_empty((cur,), self.dtype)
         self.G.zero_()
         with torch.no_grad():
             for p, o in zip(params, self.offsets):

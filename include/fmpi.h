@@ -96,6 +96,8 @@ size_t fmpi_host_symm_bytes(fmpi_host_symm* s);
 int fmpi_host_symm_free(fmpi_host_comm* c, fmpi_host_symm* s);
 int fmpi_host_allreduce_symm(fmpi_host_comm* c, fmpi_host_symm* s, size_t offset_bytes, size_t count,
                              int dtype, int op);
+int fmpi_host_bcast_symm(fmpi_host_comm* c, fmpi_host_symm* s, size_t offset_bytes, size_t nbytes,
+                         int root);
 int fmpi_host_bcast(fmpi_host_comm* c, void* buf, size_t nbytes, int root);
 /* Only root's recv is written; non-root buffers are left untouched
  * (test/test_mpi_extensions.jl:56-60). */

@@ -112,6 +112,12 @@ for dt in (torch.float32, torch.float64, torch.int32, torch.int64, torch.uint8, 
         fm.allreduce_(part, op)
         assert torch.equal(part, ref[1234:1234 + 4097]) and torch.equal(sym[:1234], src[:1234]), (dt, op)
         assert torch.equal(sym[1234 + 4097:], src[1234 + 4097:]), (dt, op)
+for root in range(w):                                       # broadcast straight out of the root's block
+    sym = fm.shm_empty((20011,), torch.float64)
+    sym.fill_(float(r))
+    fm.bcast_(sym[7:20000], root)
+    assert torch.equal(sym[7:20000], torch.full((19993,), float(root), dtype=torch.float64))
+    assert float(sym[0]) == r and float(sym[-1]) == r
 two = fm.shm_empty((3, 5), torch.float32)                   # a second block, different shape
 two.fill_(float(r + 1))
 fm.allreduce_(two, "sum")
