@@ -107,3 +107,15 @@ def test_examples_run_on_cpu(tmp_path):
     assert code == 0 and "resumed at epoch 100" in outs[0], outs[0][-3000:]
     code, outs = launch(2, [str(ROOT / "examples" / "quickstart_mlp.py")], timeout=240, env_extra=env, capture=True)
     assert code == 0, outs[0][-3000:]
+
+
+def test_doctor_passes_on_this_machine(capsys):
+    """python -m fluxmpi_b200.doctor: toolchain, libraries, a 2-rank host self-test and a
+    2-pretend-node self-test; required checks must pass on the CPU box."""
+    import json
+    from fluxmpi_b200 import doctor
+    assert doctor.main(["--json"]) == 0
+    report = json.loads(capsys.readouterr().out.strip().splitlines()[-1])
+    checks = {c["check"]: c["status"] for c in report["checks"]}
+    assert checks["libfmpi_host.so"] == "ok" and checks["host world, 2 ranks (shared memory)"] == "ok"
+    assert checks["two pretend nodes x 1 rank (TCP mesh)"] == "ok" and not report["failed"]
