@@ -27,6 +27,7 @@ import torch
 
 from . import _native, runtime
 from ._native import op_code
+from .utils import trace as _trace
 
 COMM_WORLD = "COMM_WORLD"
 
@@ -306,6 +307,10 @@ def _custom(send: torch.Tensor, recv: torch.Tensor, fn, root: int = -1):
         runtime.host_run(_host_custom_now, send.detach(), recv.detach(), fn, root)
 
 
+def _count(kind: str, t: torch.Tensor) -> None:
+    _trace.count(kind, "cuda" if t.is_cuda else "host", t.numel() * t.element_size())
+
+
 def allreduce_(v, op="sum", comm=COMM_WORLD):
     """In-place all-reduce of ``v`` with ``op``; returns ``v``.
 
@@ -316,6 +321,7 @@ def allreduce_(v, op="sum", comm=COMM_WORLD):
         raise runtime.FluxMPINotInitializedError()
     t = _as_tensor(v)
     code, fn = _resolve_op(op)
+    _count("allreduce", t)
     if fn is not None:
         _custom(t, t, fn)
         return v
@@ -333,6 +339,7 @@ def bcast_(v, root: int = 0, comm=COMM_WORLD):
         raise runtime.FluxMPINotInitializedError()
     t = _as_tensor(v)
     _check_root(root)
+    _count("bcast", t)
     if t.is_cuda:
         _device_world().bcast(t, root)
     else:
@@ -347,6 +354,7 @@ def reduce_(v, op="sum", root: int = 0, comm=COMM_WORLD):
     t = _as_tensor(v)
     code, fn = _resolve_op(op)
     _check_root(root)
+    _count("reduce", t)
     if fn is not None:
         _custom(t, t, fn, root)
         return v
@@ -385,6 +393,7 @@ def Iallreduce(*args, comm=COMM_WORLD):
     s, r = _as_tensor(send), _as_tensor(recv)
     _check_pair(s, r)
     code, fn = _resolve_op(op)
+    _count("iallreduce", r)
     if fn is not None:                      # custom function: host path, queued like the others
         if r.is_cuda:
             _custom(s, r, fn)
@@ -405,6 +414,7 @@ def Ibcast(buf, root: int = 0, comm=COMM_WORLD):
         raise runtime.FluxMPINotInitializedError()
     b = _as_tensor(buf)
     _check_root(root)
+    _count("ibcast", b)
     if b.is_cuda:
         ev = _device_world().bcast_async(b, root)
         return buf, Request(event=ev, buffer=buf)

@@ -25,6 +25,7 @@ import torch
 from .. import comm, runtime
 from .. import rules as R
 from .. import tree as T
+from ..utils import trace
 from .flat import FlatParams
 
 _tls = threading.local()
@@ -107,6 +108,8 @@ def allreduce_gradients(gs, on_gpu: bool | None = None):
         groups.setdefault((g.device, g.dtype), []).append(g)
     reqs = []
     for (dev, dt), ts in groups.items():
+        trace.count("allreduce_tree", "cuda" if dev.type == "cuda" else "host",
+                    sum(t.numel() * t.element_size() for t in ts))
         if dev.type == "cuda":
             dw = runtime.state().device_world
             if dw is not None and dw.native:

@@ -67,6 +67,23 @@ def summary() -> dict:
 def reset():
     _pending.clear()
     _records.clear()
+    _counters.clear()
+
+
+# ---- collective counters: how many calls and bytes went through each public collective, host
+# and device side separately (the reference keeps no counters or bandwidth statistics)
+_counters: dict = defaultdict(lambda: [0, 0])
+
+
+def count(kind: str, where: str, nbytes: int) -> None:
+    c = _counters[(kind, where)]
+    c[0] += 1
+    c[1] += int(nbytes)
+
+
+def counters() -> dict:
+    """{"allreduce/host": {"calls": n, "bytes": b}, "bcast/cuda": ...} for this rank."""
+    return {f"{k}/{w}": {"calls": c[0], "bytes": c[1]} for (k, w), c in sorted(_counters.items())}
 
 
 def report():

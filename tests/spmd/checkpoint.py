@@ -18,5 +18,15 @@ assert got["step"] == 7 and torch.equal(got["nested"][0], torch.arange(4.0)) and
 s = trace.summary()
 assert s["load"]["count"] == 1 and s["load"]["total_ms"] >= 0
 trace.report()
+# collective counters: calls and bytes per public collective, host and device side
+trace.reset()
+fm.allreduce_(torch.ones(10), "sum")
+fm.allreduce_(torch.ones(6, dtype=torch.float64), "max")
+fm.bcast_(torch.ones(4), 0)
+fm.allreduce_gradients({"a": torch.ones(3), "b": torch.ones(5)})
+c = trace.counters()
+assert c["allreduce/host"] == {"calls": 2, "bytes": 40 + 48}, c
+assert c["bcast/host"] == {"calls": 1, "bytes": 16}
+assert c["allreduce_tree/host"] == ({"calls": 1, "bytes": 32} if w > 1 else c["allreduce_tree/host"])
 fm.Finalize()
 print("RANK_OK", r)
