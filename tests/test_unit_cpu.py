@@ -540,3 +540,20 @@ def test_register_buffer_bookkeeping_with_mock_cuda(monkeypatch):
     with pytest.warns(UserWarning):
         assert dw.register_buffer(t) is None
     assert len(opened) == 1
+
+
+def test_launcher_helpers():
+    from fluxmpi_b200 import launch as L
+    assert not L._is_command(["train.py", "--x"], False) and not L._is_command(["pkg.mod"], True)
+    assert L._is_command(["sh", "-c", "true"], False)            # an executable on PATH runs as it is
+    assert not L._is_command(["definitely-not-a-command-xyz"], False)
+    base = L._free_port_range(4)
+    assert 1024 < base < 65535 - 4
+    with pytest.raises(ValueError):
+        L.launch(3, ["x.py"], sim_nodes=2)                        # 3 ranks do not split into 2 nodes
+    with pytest.raises(ValueError):
+        L.launch(2, ["x.py"], nnodes=2)                           # multi-node needs an explicit port
+    # a command (not a python script) is started as it is, with the rank environment
+    code, outs = L.launch(2, ["sh", "-c", "echo rank=$RANK/$WORLD_SIZE local=$LOCAL_RANK node=$GROUP_RANK"],
+                          capture=True, timeout=60, sim_nodes=2)
+    assert code == 0 and outs[0].strip() == "rank=0/2 local=0 node=0" and outs[1].strip() == "rank=1/2 local=0 node=1"
