@@ -56,10 +56,12 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--out", default="")
+    ap.add_argument("--variant", type=int, default=0, help="0: one SM per tile, 1: CTA pairs (cta_group::2)")
     a = ap.parse_args()
     assert torch.cuda.is_available()
     if conv_bn.gemm_lib() is None:
         raise SystemExit("libfmpi_gemm.so unavailable: " + str(conv_bn.why_unavailable()))
+    conv_bn.set_variant(a.variant)
     dev = torch.device("cuda", 0)
     rows, tot = [], {"cudnn_fwd": 0.0, "fused_fwd": 0.0, "cudnn_fwdbwd": 0.0, "fused_fwdbwd": 0.0}
     for hw, cin, cout, relu, res, count in SHAPES:

@@ -63,14 +63,23 @@ struct keep_first {
 
 constexpr auto kRound = cutlass::FloatRoundStyle::round_to_nearest;
 
-template <int kTileN>
+// k2Sm = false: one SM per 128 x kTileN tile (CTA tile == MMA tile).
+// k2Sm = true:  the CTA pair of a cluster shares one 256 x kTileN MMA tile (tcgen05
+//               cta_group::2): each CTA still owns a 128 x kTileN accumulator and epilogue, the W
+//               tile is loaded once for both.
+template <int kTileN, bool k2Sm>
 struct PointwiseConvStats {
   using Element = cutlass::bfloat16_t;
-  using TileShape = Shape<_128, Int<kTileN>, _64>;     // one SM per tile: CTA tile == MMA tile
-  using ClusterShape = Shape<_1, _1, _1>;
+  using CtaTile = Shape<_128, Int<kTileN>, _64>;
+  using TileShape = cute::conditional_t<k2Sm, Shape<_256, Int<kTileN>, _64>, CtaTile>;   // MMA tile
+  using ClusterShape = cute::conditional_t<k2Sm, Shape<_2, _1, _1>, Shape<_1, _1, _1>>;
+  using EpilogueSchedule = cute::conditional_t<k2Sm, cutlass::epilogue::TmaWarpSpecialized2Sm,
+                                               cutlass::epilogue::TmaWarpSpecialized1Sm>;
+  using MainloopSchedule = cute::conditional_t<k2Sm, cutlass::gemm::KernelTmaWarpSpecialized2SmSm100,
+                                               cutlass::gemm::KernelTmaWarpSpecialized1SmSm100>;
   static constexpr int kAlign = 128 / cutlass::sizeof_bits<Element>::value;
 
-  using RowSum = fus::Sm90RowReduction<cutlass::plus, cutlass::plus, cutlass::atomic_add, 0, TileShape,
+  using RowSum = fus::Sm90RowReduction<cutlass::plus, cutlass::plus, cutlass::atomic_add, 0, CtaTile,
                                        float, float, kRound>;
   using Square = fus::Sm90EVT<fus::Sm90Compute<cutlass::multiplies, float, float, kRound>,
                               fus::Sm90AccFetch, fus::Sm90AccFetch>;
@@ -83,7 +92,7 @@ struct PointwiseConvStats {
       cutlass::epilogue::collective::EpilogueTileAuto, float, float,
       void, cutlass::layout::RowMajor, kAlign,                    // no source tensor
       Element, cutlass::layout::RowMajor, kAlign,
-      cutlass::epilogue::TmaWarpSpecialized1Sm, Tree>::CollectiveOp;
+      EpilogueSchedule, Tree>::CollectiveOp;
 
   using Mainloop = typename cutlass::gemm::collective::CollectiveBuilder<
       cutlass::arch::Sm100, cutlass::arch::OpClassTensorOp,
@@ -91,7 +100,7 @@ struct PointwiseConvStats {
       Element, cutlass::layout::ColumnMajor, kAlign,              // W: [N, K], K contiguous
       float, TileShape, ClusterShape,
       cutlass::gemm::collective::StageCountAutoCarveout<static_cast<int>(sizeof(typename Epilogue::SharedStorage))>,
-      cutlass::gemm::KernelTmaWarpSpecialized1SmSm100>::CollectiveOp;
+      MainloopSchedule>::CollectiveOp;
 
   using Kernel = cutlass::gemm::kernel::GemmUniversal<Shape<int, int, int, int>, Mainloop, Epilogue>;
   using Gemm = cutlass::gemm::device::GemmUniversalAdapter<Kernel>;
@@ -141,13 +150,24 @@ extern "C" {
 
 const char* fmpi_gemm_last_error(void) { return g_gemm_err.c_str(); }
 
-// One tile shape, 128 x 64 x 64: every thread of the four epilogue warps then keeps 64 + 64
+// CTA tiles are 128 x 64 x 64: every thread of the four epilogue warps then keeps 64 + 64
 // partial column sums in registers (a 128-wide tile needs 256 and spills; see -Xptxas -v).
 // The layers this serves are bandwidth-bound, so the narrower tile costs L2 re-reads of X only.
-using ConvStats = PointwiseConvStats<64>;
+// Two variants to time against each other: 0 = one SM per tile, 1 = CTA pairs (cta_group::2).
+using ConvStats1Sm = PointwiseConvStats<64, false>;
+using ConvStats2Sm = PointwiseConvStats<64, true>;
+static int g_variant = 0;
+
+int fmpi_conv1x1_bnstats_variant(int variant) {
+  if (variant < 0 || variant > 1) return gemm_fail("fmpi_conv1x1_bnstats_variant", "0 (1 SM) or 1 (2 SM)");
+  g_variant = variant;
+  return 0;
+}
 
 // Bytes of device workspace fmpi_conv1x1_bnstats needs for this problem (may be 0).
-size_t fmpi_conv1x1_bnstats_workspace(int M, int N, int K) { return ConvStats::workspace_bytes(M, N, K); }
+size_t fmpi_conv1x1_bnstats_workspace(int M, int N, int K) {
+  return g_variant ? ConvStats2Sm::workspace_bytes(M, N, K) : ConvStats1Sm::workspace_bytes(M, N, K);
+}
 
 // y[M, N] = x[M, K] * w[N, K]^T (all bf16, row-major, 16-byte aligned rows: K % 8 == 0 and
 // N % 8 == 0); sum[N] and sqs[N] (fp32) receive the per-column sum and sum of squares of the
@@ -157,7 +177,9 @@ int fmpi_conv1x1_bnstats(const void* x, const void* w, void* y, float* sum, floa
   if (!x || !w || !y || !sum || !sqs) return gemm_fail("fmpi_conv1x1_bnstats", "null argument");
   if (M <= 0 || N <= 0 || K <= 0 || (N % 8) || (K % 8))
     return gemm_fail("fmpi_conv1x1_bnstats", "need M, N, K > 0 with N and K multiples of 8");
-  return ConvStats::run(x, w, y, sum, sqs, M, N, K, workspace, workspace_bytes, static_cast<cudaStream_t>(stream));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return g_variant ? ConvStats2Sm::run(x, w, y, sum, sqs, M, N, K, workspace, workspace_bytes, st)
+                   : ConvStats1Sm::run(x, w, y, sum, sqs, M, N, K, workspace, workspace_bytes, st);
 }
 
 }  // extern "C"

@@ -46,10 +46,23 @@ def gemm_lib():
         lib.fmpi_conv1x1_bnstats_workspace.argtypes = [C.c_int, C.c_int, C.c_int]
         lib.fmpi_conv1x1_bnstats.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                              C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
+        lib.fmpi_conv1x1_bnstats_variant.argtypes = [C.c_int]
+        # FMPI_CONV_BN_VARIANT=1 selects the CTA-pair (cta_group::2) kernel; see set_variant
+        if lib.fmpi_conv1x1_bnstats_variant(int(os.environ.get("FMPI_CONV_BN_VARIANT", "0") or 0)):
+            raise OSError(lib.fmpi_gemm_last_error().decode(errors="replace"))
         _lib = lib
     except OSError as e:
         _lib_failed = str(e)
     return _lib
+
+
+def set_variant(variant: int) -> None:
+    """0: one SM per 128x64 tile (default); 1: CTA pairs sharing a 256x64 MMA tile."""
+    lib = gemm_lib()
+    if lib is None:
+        raise _native.NativeError("libfmpi_gemm.so unavailable: " + str(_lib_failed))
+    if lib.fmpi_conv1x1_bnstats_variant(int(variant)):
+        raise ValueError(lib.fmpi_gemm_last_error().decode(errors="replace"))
 
 
 def why_unavailable() -> Optional[str]:

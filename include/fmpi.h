@@ -332,6 +332,8 @@ int fmpi_bn_forward_presummed(const void* x, const void* res, void* y, uint64_t 
  *   y[M, N] = x[M, K] * w[N, K]^T  (bf16, row-major; N and K multiples of 8)
  *   sum[N], sqs[N] (fp32) = column sums of the fp32 accumulators and of their squares.
  * EXPERIMENTAL: compiled and inspected, not yet run on a GPU; nothing uses it by default. */
+/* variant 0 (default): one SM per 128x64 tile; 1: CTA pairs on a 256x64 MMA tile (cta_group::2) */
+int fmpi_conv1x1_bnstats_variant(int variant);
 size_t fmpi_conv1x1_bnstats_workspace(int M, int N, int K);
 int fmpi_conv1x1_bnstats(const void* x, const void* w, void* y, float* sum, float* sqs, int M, int N,
                          int K, void* workspace, size_t workspace_bytes, fmpi_stream st);

@@ -18,6 +18,9 @@ lib.fmpi_conv1x1_bnstats_workspace.restype = C.c_size_t
 lib.fmpi_conv1x1_bnstats_workspace.argtypes = [C.c_int] * 3
 lib.fmpi_gemm_last_error.restype = C.c_char_p
 lib.fmpi_conv1x1_bnstats.argtypes = [C.c_void_p] * 5 + [C.c_int] * 3 + [C.c_void_p, C.c_size_t, C.c_void_p]
+lib.fmpi_conv1x1_bnstats_variant.argtypes = [C.c_int]
+assert lib.fmpi_conv1x1_bnstats_variant(int(sys.argv[3])) == 0
+assert lib.fmpi_conv1x1_bnstats_variant(7) == 1            # unknown variant refused, selection kept
 out = []
 for M, N, K in json.loads(sys.argv[2]):
     ws = lib.fmpi_conv1x1_bnstats_workspace(M, N, K)
@@ -27,7 +30,8 @@ print(json.dumps(out))
 """
 
 
-def test_host_side_checks_with_a_stub_driver(tmp_path):
+@pytest.mark.parametrize("variant", [0, 1], ids=["1sm", "2sm"])
+def test_host_side_checks_with_a_stub_driver(tmp_path, variant):
     import json
     from fluxmpi_b200 import _build
     lib = _build.build_gemm()
@@ -45,7 +49,7 @@ def test_host_side_checks_with_a_stub_driver(tmp_path):
                (28, 512, 256), (14, 1024, 256), (14, 256, 1024), (14, 1024, 512), (7, 2048, 512), (7, 512, 2048)]]
     shapes += [(147, 64, 64), (128, 64, 16), (100, 60, 64), (100, 64, 12)]
     env = dict(os.environ, LD_LIBRARY_PATH=f"{tmp_path}:{os.environ.get('LD_LIBRARY_PATH', '')}")
-    r = subprocess.run([sys.executable, "-c", PROBE, str(lib), json.dumps(shapes)], env=env,
+    r = subprocess.run([sys.executable, "-c", PROBE, str(lib), json.dumps(shapes), str(variant)], env=env,
                        capture_output=True, text=True, timeout=120)
     assert r.returncode == 0, r.stderr[-2000:]
     res = json.loads(r.stdout.strip().splitlines()[-1])

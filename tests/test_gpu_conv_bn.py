@@ -27,10 +27,19 @@ def test_library_loads():
     assert conv_bn.gemm_lib() is not None, conv_bn.why_unavailable()
 
 
+@pytest.fixture(autouse=True)
+def _default_variant():
+    yield
+    if conv_bn.gemm_lib() is not None:
+        conv_bn.set_variant(0)
+
+
+@pytest.mark.parametrize("variant", [0, 1], ids=["1sm", "2sm"])
 @pytest.mark.parametrize("M,N,K", [(128, 64, 64), (147, 64, 64), (4096, 256, 64), (3000, 128, 512), (25088, 64, 256)])
-def test_gemm_and_column_sums(M, N, K):
+def test_gemm_and_column_sums(M, N, K, variant):
     torch.manual_seed(0)
     lib = conv_bn.gemm_lib()
+    conv_bn.set_variant(variant)
     x = torch.randn(M, K, device="cuda").bfloat16()
     w = (torch.randn(N, K, device="cuda") / K ** 0.5).bfloat16()
     y = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
