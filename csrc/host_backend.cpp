@@ -383,10 +383,15 @@ int fmpi_host_init(const char* name, int rank, int world, size_t slot_bytes, dou
     shm_unlink(name);  // stale segment from a crashed job with the same name
     fd = shm_open(name, O_CREAT | O_EXCL | O_RDWR, 0600);
     if (fd < 0) { delete c; return fail("shm_open(create %s): %s", name, strerror(errno)); }
-    if (ftruncate(fd, off_t(c->map_bytes)) != 0) {
-      const int e = errno;
-      close(fd); shm_unlink(name); delete c;
-      return fail("ftruncate: %s", strerror(e));
+    // allocate the pages now: on a machine whose /dev/shm is too small (64 MB is a common
+    // container default) this is an error message here instead of a SIGBUS at the first touch
+    const int e = posix_fallocate(fd, 0, off_t(c->map_bytes));
+    if (e != 0) {
+      close(fd); shm_unlink(name);
+      const size_t need = c->map_bytes;
+      delete c;
+      return fail("cannot allocate %zu bytes of shared memory for the host world: %s "
+                  "(is /dev/shm large enough? lower Init(slot_bytes=...) or enlarge it)", need, strerror(e));
     }
   } else {
     Backoff b;
@@ -767,7 +772,7 @@ int fmpi_host_symm_alloc(fmpi_host_comm* c, size_t nbytes, fmpi_host_symm** out)
     if (create) shm_unlink(nm.c_str());
     const int fd = shm_open(nm.c_str(), create ? (O_CREAT | O_EXCL | O_RDWR) : O_RDWR, 0600);
     if (fd < 0) return nullptr;
-    if (create && ftruncate(fd, off_t(bytes)) != 0) { close(fd); return nullptr; }
+    if (create && posix_fallocate(fd, 0, off_t(bytes)) != 0) { close(fd); return nullptr; }  // see fmpi_host_init
     void* p = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
     close(fd);
     return p == MAP_FAILED ? nullptr : static_cast<uint8_t*>(p);
