@@ -369,7 +369,7 @@ def update(state_tree, params, grads):
     hook = getattr(_first_rule(state_tree), "tree_update", None)
     if hook is not None:
         return hook(state_tree, params, grads, False)
-    return _walk_update(state_tree, params, grads, False, {})
+    return walk_update(state_tree, params, grads, False)
 
 
 def update_(state_tree, params, grads):
@@ -393,7 +393,33 @@ def walk_update(state_tree, params, grads, inplace: bool):
         from .ops import host_rules
         if host_rules.try_tree_step_host_(state_tree, params, grads):
             return state_tree, params
+    elif not _any_cuda(params) and _first_rule(state_tree) is not None:
+        # non-mutating step on CPU leaves: copy parameters and state once, then the native loop
+        # on the copies (3 copies + 1 pass instead of ~13 out-of-place passes per Adam leaf)
+        from .ops import host_rules
+        if host_rules._host_hyper(_first_rule(state_tree)) is not None:
+            new_st, new_ps = _copy_for_step(state_tree, params)
+            if host_rules.try_tree_step_host_(new_st, new_ps, grads):
+                return new_st, new_ps
     return _walk_update(state_tree, params, grads, inplace, {})
+
+
+def _copy_for_step(state_tree, params):
+    """Fresh Leafs with cloned state tensors and detached clones of the trainable parameters;
+    ties are kept (a shared Leaf / tensor is copied once), everything else is passed through."""
+    leaf_cache: dict[int, Leaf] = {}
+
+    def copy_leaf(n):
+        if not isinstance(n, Leaf):
+            return n
+        if id(n) not in leaf_cache:
+            state = T.fmap(lambda t: t.clone() if isinstance(t, torch.Tensor) else t, n.state)
+            leaf_cache[id(n)] = Leaf(n.rule, state, n.frozen)
+        return leaf_cache[id(n)]
+
+    new_st = T.fmap(copy_leaf, state_tree, is_leaf=_is_leaf_node)
+    new_ps = T.fmap(lambda x: _data(x).clone() if _trainable(x) else x, params)
+    return new_st, new_ps
 
 
 def _any_cuda(params) -> bool:

@@ -557,3 +557,29 @@ def test_launcher_helpers():
     code, outs = L.launch(2, ["sh", "-c", "echo rank=$RANK/$WORLD_SIZE local=$LOCAL_RANK node=$GROUP_RANK"],
                           capture=True, timeout=60, sim_nodes=2)
     assert code == 0 and outs[0].strip() == "rank=0/2 local=0 node=0" and outs[1].strip() == "rank=1/2 local=0 node=1"
+
+
+@pytest.mark.parametrize("rule", [R.Momentum(0.01, 0.9), R.Adam(1e-3), R.AdamW(1e-3, (0.9, 0.99), 1e-3), R.RMSProp(1e-3)],
+                         ids=["momentum", "adam", "adamw", "rmsprop"])
+def test_non_mutating_update_on_cpu_uses_copies_and_matches_per_leaf_ops(rule):
+    """``update`` (Optimisers.update, the call in the reference's README) on CPU leaves: the
+    native loop runs on copies; inputs stay untouched, ties stay tied, numbers equal the
+    per-leaf path; a rule without a native loop simply takes the per-leaf path."""
+    import copy
+    torch.manual_seed(0)
+    ps = {"a": torch.randn(65, 9), "b": {"w": torch.randn(100), "k": 3}}
+    ps["b"]["tied"] = ps["b"]["w"]
+    ps0 = copy.deepcopy(ps)
+    st, st2 = R.setup(rule, ps), R.setup(rule, ps)
+    st_first = st
+    a, b = ps, ps
+    for _ in range(4):
+        gs = {"a": torch.randn(65, 9), "b": {"w": torch.randn(100), "k": None}}
+        gs["b"]["tied"] = gs["b"]["w"]
+        st, a = R.update(st, a, gs)
+        st2, b = R._walk_update(st2, b, gs, False, {})
+    assert torch.equal(ps["a"], ps0["a"]) and torch.equal(ps["b"]["w"], ps0["b"]["w"])      # inputs untouched
+    assert T.tree_equal(st_first["a"].state, R.setup(rule, ps)["a"].state)                   # first state untouched
+    assert a["b"]["tied"] is a["b"]["w"] and a["b"]["k"] == 3 and st["b"]["tied"] is st["b"]["w"]
+    assert torch.allclose(a["a"], b["a"], rtol=1e-6, atol=1e-7) and torch.allclose(a["b"]["w"], b["b"]["w"], rtol=1e-6, atol=1e-7)
+    assert T.tree_equal(st["a"].state, st2["a"].state) or torch.allclose(st["a"].state[0], st2["a"].state[0], rtol=1e-6, atol=1e-7)
