@@ -154,6 +154,20 @@ def shm_empty(shape, dtype=torch.float32) -> torch.Tensor:
     return torch.frombuffer(buf, dtype=dtype, count=numel).view(shape)
 
 
+def shm_free(t: torch.Tensor) -> None:
+    """Collective: give back the block a tensor from :func:`shm_empty` lives in (call it on every
+    rank, in the same order; the tensor and its views must not be used afterwards). Blocks that
+    are never freed are released by ``Finalize``."""
+    S = runtime.state()
+    p = t.data_ptr()
+    for i, (lo, hi, h, _buf) in enumerate(S.host_symm):
+        if lo <= p < hi:
+            del S.host_symm[i]
+            runtime.host_run(lambda: _native.host_check(
+                _native.host().fmpi_host_symm_free(S.host_comm, h), "host_symm_free"))
+            return
+
+
 def _host_symm_hit(t: torch.Tensor):
     """(segment handle, byte offset) when ``t`` lies inside a block from :func:`shm_empty`."""
     regs = runtime.state().host_symm

@@ -122,6 +122,11 @@ two = fm.shm_empty((3, 5), torch.float32)                   # a second block, di
 two.fill_(float(r + 1))
 fm.allreduce_(two, "sum")
 assert torch.equal(two, torch.full((3, 5), w * (w + 1) / 2))
+fm.shm_free(two)                                            # collective; later blocks still work
+three = fm.shm_empty((9,), torch.int64)
+three.fill_(r)
+fm.allreduce_(three, "max")
+assert torch.equal(three, torch.full((9,), w - 1))
 
 # a gradient tree as ONE message: leaves of odd sizes that straddle the 64 KB slots, compared
 # bit for bit with one all-reduce per leaf
