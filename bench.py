@@ -50,9 +50,6 @@ def parse():
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--no-fused-bn", action="store_true",
                     help="ours: use stock nn.BatchNorm2d + ReLU instead of the fused channels-last kernels")
-    ap.add_argument("--conv-bn", action="store_true",
-                    help="ours (experimental): 1x1 convolutions as tcgen05 GEMMs that also take the "
-                         "BatchNorm statistics (ops/conv_bn.py)")
     ap.add_argument("--bucket-mb", type=float, default=32.0)
     ap.add_argument("--algo", default="auto")
     return ap.parse_args()
@@ -110,12 +107,12 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------ shared pieces
-def make_model(name, fused_bn=False, fused_conv_bn=False):
+def make_model(name, fused_bn=False):
     """Same architecture, parameters and initialisation in both arms. ``fused_bn`` swaps the
     BatchNorm2d / ReLU / residual-add modules for the framework's channels-last kernels (our
     arm); the DDP arm always runs the stock PyTorch modules."""
     from fluxmpi_b200.models import resnet50, resnet_tiny
-    kw = dict(fused_bn=fused_bn, fused_conv_bn=fused_conv_bn)
+    kw = dict(fused_bn=fused_bn)
     return resnet50(**kw) if name == "resnet50" else resnet_tiny(1000, **kw)
 
 
@@ -212,8 +209,7 @@ def run_ours(a):
     cdt = torch.bfloat16 if a.dtype == "bf16" else torch.float32
 
     torch.manual_seed(rank)
-    model = make_model(a.model, fused_bn=not a.no_fused_bn,
-                       fused_conv_bn=a.conv_bn).to(dev).to(memory_format=torch.channels_last)
+    model = make_model(a.model, fused_bn=not a.no_fused_bn).to(dev).to(memory_format=torch.channels_last)
     engine = DataParallelEngine(model, fm.DistributedOptimizer(R.Adam(1e-3)), bucket_mb=a.bucket_mb,
                                 overlap=not a.no_overlap, algo=a.algo)
     inv_w = 1.0 / world                        # reference semantics: SUM, loss scaled by 1/W
@@ -314,7 +310,6 @@ def run_ours(a):
                        "seq_len": None, "parallelism": f"dp{world}", "optimizer": "Adam(1e-3), fused with the gradient all-reduce",
                        "layout": "channels_last", "cuda_graph": not a.no_graph, "overlap": not a.no_overlap,
                        "batchnorm": "stock nn.BatchNorm2d" if a.no_fused_bn else "fused channels-last BN(+add)(+ReLU) kernels (ours)",
-                       "conv1x1_bn_stats_fusion": bool(a.conv_bn),
                        "bucket_mb": a.bucket_mb, "buckets": len(engine.buckets),
                        "comm": f"{dw.mode}{'+nvls' if engine.algo == _native.ALGO_NVLS else ''}",
                        "l2": "per-step working set (activations of 256 images + 205 MB of parameters and gradients) far exceeds the 126 MB L2; no explicit flush",

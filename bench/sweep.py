@@ -75,10 +75,7 @@ def main():
     ap.add_argument("--no-nccl", action="store_true")
     ap.add_argument("--graph", action="store_true", help="time CUDA-graph replays (no host launch cost)")
     ap.add_argument("--symm", action="store_true", help="our buffers come from fm.symm_empty (registered memory)")
-    ap.add_argument("--register", action="store_true",
-                    help="ordinary tensors registered with fm.register_buffer (CUDA IPC, experimental)")
     a = ap.parse_args()
-    regs = []
 
     fm.Init()
     r, w = fm.local_rank(), fm.total_workers()
@@ -110,10 +107,6 @@ def main():
             bufs = symm_pool[nbytes]
             for b in bufs:
                 b.fill_(1)
-        elif a.register:  # ordinary tensors mapped into the peers through CUDA IPC (experimental)
-            nbuf = max(1, min(nbuf, 4))
-            bufs = [torch.ones(n, dtype=dt, device=dev) for _ in range(nbuf)]
-            regs = [fm.register_buffer(b) for b in bufs] if nbytes % 16 == 0 else []
         else:
             bufs = [torch.ones(n, dtype=dt, device=dev) for _ in range(nbuf)]
         iters = 200 if nbytes <= (1 << 20) else 40 if nbytes <= (64 << 20) else 10
@@ -147,10 +140,6 @@ def main():
         rows.append(row)
         if r == 0:
             print(json.dumps(row), flush=True)
-        if a.register:
-            for g in regs:
-                fm.deregister_buffer(g)
-            regs = []
         del bufs
         torch.cuda.empty_cache()
     if r == 0 and a.out:

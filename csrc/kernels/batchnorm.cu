@@ -379,7 +379,7 @@ size_t bn_scratch_floats(int C) { return size_t(kBNMaxGx) * 2 * C + 5 * size_t(C
 template <typename T>
 int bn_forward_t(const void* x, const void* res, void* y, uint64_t M, int C, const float* gamma, const float* beta,
                  float* rmean, float* rvar, float momentum, float eps, int relu, float* save_mean,
-                 float* save_invstd, float* scratch, cudaStream_t st, bool presummed = false) {
+                 float* save_invstd, float* scratch, cudaStream_t st) {
   constexpr int N = VecOps<T>::kN;
   const BNGeom g = bn_geom(M, C / N);
   float* partial = scratch;
@@ -387,11 +387,8 @@ int bn_forward_t(const void* x, const void* res, void* y, uint64_t M, int C, con
   float* shift = scale + C;
   const dim3 grid(g.gx, g.gy);
   const size_t smem = size_t(kBNThreads) * 2 * N * sizeof(float);
-  // presummed: the producer of x (csrc/kernels/gemm_bnstats.cu) already left the column sums in
-  // partial[0][0][:] and the sums of squares in partial[0][1][:], so the pass over x is skipped
-  if (!presummed)
-    bn_stats_kernel<T><<<grid, kBNThreads, smem, st>>>(static_cast<const T*>(x), M, C, g.tx, g.rows_per_cta, partial);
-  bn_fwd_finalize_kernel<<<(C + kFoldC - 1) / kFoldC, dim3(kFoldC, kFoldG), 0, st>>>(partial, presummed ? 1u : g.gx, M, C, gamma, beta, rmean, rvar, momentum,
+  bn_stats_kernel<T><<<grid, kBNThreads, smem, st>>>(static_cast<const T*>(x), M, C, g.tx, g.rows_per_cta, partial);
+  bn_fwd_finalize_kernel<<<(C + kFoldC - 1) / kFoldC, dim3(kFoldC, kFoldG), 0, st>>>(partial, g.gx, M, C, gamma, beta, rmean, rvar, momentum,
                                                           eps, save_mean, save_invstd, scale, shift);
   const T* xp = static_cast<const T*>(x);
   const T* rp = static_cast<const T*>(res);
@@ -480,23 +477,6 @@ int fmpi_bn_forward(const void* x, const void* res, void* y, uint64_t M, int C, 
     case FMPI_F32: return bn_forward_t<float>(x, res, y, M, C, gamma, beta, running_mean, running_var, momentum, eps, relu, save_mean, save_invstd, sc, s);
     case FMPI_BF16: return bn_forward_t<__nv_bfloat16>(x, res, y, M, C, gamma, beta, running_mean, running_var, momentum, eps, relu, save_mean, save_invstd, sc, s);
     default: return bn_forward_t<__half>(x, res, y, M, C, gamma, beta, running_mean, running_var, momentum, eps, relu, save_mean, save_invstd, sc, s);
-  }
-}
-
-// fmpi_bn_forward without the statistics pass: the first 2*C floats of `scratch` already hold the
-// per-channel sum and sum of squares of x (written by fmpi_conv1x1_bnstats, which produced x).
-int fmpi_bn_forward_presummed(const void* x, const void* res, void* y, uint64_t M, int C, int dtype,
-                              const float* gamma, const float* beta, float* running_mean, float* running_var,
-                              float momentum, float eps, int relu, float* save_mean, float* save_invstd,
-                              void* scratch, fmpi_stream st) {
-  if (bn_check(M, C, dtype, x, y)) return 1;
-  if (!save_mean || !save_invstd || !scratch) return set_error("batch norm: null output / scratch");
-  cudaStream_t s = static_cast<cudaStream_t>(st);
-  float* sc = static_cast<float*>(scratch);
-  switch (dtype) {
-    case FMPI_F32: return bn_forward_t<float>(x, res, y, M, C, gamma, beta, running_mean, running_var, momentum, eps, relu, save_mean, save_invstd, sc, s, true);
-    case FMPI_BF16: return bn_forward_t<__nv_bfloat16>(x, res, y, M, C, gamma, beta, running_mean, running_var, momentum, eps, relu, save_mean, save_invstd, sc, s, true);
-    default: return bn_forward_t<__half>(x, res, y, M, C, gamma, beta, running_mean, running_var, momentum, eps, relu, save_mean, save_invstd, sc, s, true);
   }
 }
 

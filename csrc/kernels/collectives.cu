@@ -28,6 +28,8 @@
 // them (the asm loads are volatile, so the batch is what puts requests in flight).
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <string>
 
 #include "common.cuh"
@@ -51,6 +53,62 @@ int check_cuda(cudaError_t e, const char* what) {
 
 extern "C" const char* fmpi_cuda_last_error(void) { return fmpi_host::g_err.c_str(); }
 extern "C" size_t fmpi_sigpad_bytes(void) { return fmpi::kSigPadBytes; }
+
+// ---- health page: pinned + mapped, one per device of this process
+#include <mutex>
+namespace {
+struct HealthPage { uint32_t* host = nullptr; uint32_t* dev = nullptr; };
+HealthPage g_health[64];
+std::mutex g_health_mu;
+int health_for_current(HealthPage** out) {
+  int dev = 0;
+  if (fmpi_host::check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return 1;
+  if (dev < 0 || dev >= 64) return fmpi_host::set_error("device index %d out of range", dev);
+  std::lock_guard<std::mutex> lk(g_health_mu);
+  HealthPage& h = g_health[dev];
+  if (!h.host) {
+    void* p = nullptr;
+    if (fmpi_host::check_cuda(cudaHostAlloc(&p, 64, cudaHostAllocMapped | cudaHostAllocPortable), "cudaHostAlloc(health page)")) return 1;
+    memset(p, 0, 64);
+    void* d = nullptr;
+    if (fmpi_host::check_cuda(cudaHostGetDevicePointer(&d, p, 0), "cudaHostGetDevicePointer")) { cudaFreeHost(p); return 1; }
+    h.host = static_cast<uint32_t*>(p);
+    h.dev = static_cast<uint32_t*>(d);
+  }
+  *out = &h;
+  return 0;
+}
+}  // namespace
+extern "C" int fmpi_health_page(uint32_t** host_ptr, uint32_t** dev_ptr) {
+  HealthPage* h;
+  if (health_for_current(&h)) return 1;
+  if (host_ptr) *host_ptr = h->host;
+  if (dev_ptr) *dev_ptr = h->dev;
+  return 0;
+}
+extern "C" int fmpi_health_check(void) {
+  HealthPage* h;
+  if (health_for_current(&h)) return 1;
+  const volatile uint32_t* w = h->host;
+  if (w[fmpi::kCtrlError])
+    return fmpi_host::set_error("a cross-GPU wait was abandoned after its time budget: a peer rank is lost or "
+                                "far behind (results of the collectives in flight are undefined)");
+  if (w[fmpi::kCtrlAbort]) return fmpi_host::set_error("the device world was aborted by the host");
+  return 0;
+}
+extern "C" int fmpi_health_abort(void) {
+  HealthPage* h;
+  if (health_for_current(&h)) return 1;
+  reinterpret_cast<volatile uint32_t*>(h->host)[fmpi::kCtrlAbort] = 1;
+  return 0;
+}
+extern "C" int fmpi_health_reset(void) {
+  HealthPage* h;
+  if (health_for_current(&h)) return 1;
+  reinterpret_cast<volatile uint32_t*>(h->host)[fmpi::kCtrlAbort] = 0;
+  reinterpret_cast<volatile uint32_t*>(h->host)[fmpi::kCtrlError] = 0;
+  return 0;
+}
 
 namespace fmpi {
 
@@ -324,7 +382,31 @@ bcast_symm_kernel(fmpi_devcomm c, uint64_t off, uint64_t nvec, int root, int mod
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
   const uint64_t t0 = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
   const uint8_t* src = byte_ptr(c.data[x.rank], off);
-  if (mode != 1) {
+  if (mode == 3) {
+    // pull + re-emit: rank q loads slice q from the ROOT's window (the root's link carries the
+    // message once, spread over W-1 readers) and stores it to every other rank — through the
+    // multicast alias when there is one — so all W links send at once. The root's own slice is
+    // emitted by the root. No barrier between the two steps: a vector is re-emitted by the
+    // thread that fetched it.
+    const uint64_t per = ceil_div(nvec, c.world);
+    const uint64_t lo = min(per * x.rank, nvec), hi = min(lo + per, nvec);
+    const uint8_t* rsrc = byte_ptr(c.data[root], off);
+    const int me = x.rank;
+    if (c.mc_data && !c.emulate) {
+      uint8_t* mc = byte_ptr(c.mc_data, off);
+      vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_stream(rsrc + j * 16); },
+                  [&](uint64_t j, uint4 v) { multimem_st(mc + j * 16, v); });
+    } else {
+      vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_stream(rsrc + j * 16); },
+                  [&](uint64_t j, uint4 v) {
+#pragma unroll
+                    for (int r = 0; r < FMPI_MAX_RANKS; ++r)
+                      if (r < c.world && r != root) st_stream(byte_ptr(c.data[r], off) + j * 16, v);
+                    (void)me;
+                  });
+    }
+    block_barrier(x, c);
+  } else if (mode != 1) {
     if (x.rank == root) {
       if (mode == 2) {
         uint8_t* mc = byte_ptr(c.mc_data, off);
@@ -452,6 +534,181 @@ bcast_stage_kernel(fmpi_devcomm c, PtrTable buf, uint64_t nbytes, int root, uint
   ctx_finish(x);
 }
 
+// ---------------------------------------------------------------------------- chunk pipeline
+// Large messages in ordinary (unregistered) buffers. One persistent kernel per rank whose CTAs
+// take one of three roles and hand chunks to each other through counters and cross-GPU flags,
+// so the staging copies run UNDER the link phase instead of before and after it:
+//
+//   in    copy chunk k of the user buffer into staging slot k % S       (local HBM traffic)
+//         (bcast: the root pushes slice q of the chunk straight into rank q's slot)
+//   link  on slot k % S, owner of slice q: multimem.ld_reduce + multimem.st (in-switch sum and
+//         multicast) or W peer loads + W peer stores; reduce: result to the root's slot only;
+//         bcast: re-emit my slice to everybody
+//   out   copy slot k % S into the user buffer                            (local HBM traffic)
+//
+// Per slot s and use u (= k / S) the hand-over values are U = base[s] + u + 1 (base[s] = uses of
+// the slot in all earlier calls, so flags only ever grow):
+//   in  -> link : every rank's flag[IN][s]   >= U   (all ranks copied chunk k in)
+//   link -> out : every rank's flag[LINK][s] >= U   (all slices of chunk k reduced and landed)
+//   out -> in   : flag[LINK][s] >= U on every rank (peers no longer read my slot) and my own
+//                 out-counter; bcast: flag[OUT][s] >= U from every receiver
+// A role's CTAs count themselves done per slot; the one that completes the count signals.
+// All CTAs are co-resident (grid <= SM count), so the waits cannot deadlock.
+struct PipeArgs {
+  PtrTable in, out;
+  uint64_t nvec, chunk_vec, stage_off;
+  int nslots, kind, root, op;   // kind: 0 all-reduce, 1 reduce to root, 2 broadcast from root
+  int n_link, n_copy;           // CTAs in the link role; the rest are split over in / out
+};
+enum { kPipeIn = 0, kPipeLink = 1, kPipeOut = 2 };
+
+template <typename T, bool kNvls>
+__global__ void __launch_bounds__(512)
+pipe_kernel(fmpi_devcomm c, PipeArgs a) {
+  Ctx x;
+  ctx_init(x, c);
+  const int ai = arg_index(c);
+  const int me = x.rank, W = c.world, S = a.nslots;
+  const uint8_t* src = static_cast<const uint8_t*>(a.in.p[ai]);
+  uint8_t* dst = static_cast<uint8_t*>(a.out.p[ai]);
+  uint32_t* pad = x.my_pad;
+  __shared__ uint32_t base_s[kPipeSlots];
+  __shared__ uint32_t last_s;
+  if (threadIdx.x < kPipeSlots) base_s[threadIdx.x] = pad[kCtlBase + kCtlPipeBase + threadIdx.x];
+  // every rank has entered this call => every rank has left the previous one on this channel
+  block_barrier(x, c);
+
+  // ---- roles (the grid is the same on every rank; what a copy CTA does depends on the rank)
+  const bool has_in = a.kind != 2 || me == a.root;
+  const bool has_out = a.kind == 0 || (a.kind == 1 ? me == a.root : me != a.root);
+  const int n_in = has_in ? (has_out ? a.n_copy / 2 : a.n_copy) : 0;
+  const int n_out = has_out ? a.n_copy - n_in : 0;
+  int role, idx, nrole;
+  if (int(blockIdx.x) < a.n_link) { role = kPipeLink; idx = blockIdx.x; nrole = a.n_link; }
+  else if (int(blockIdx.x) - a.n_link < n_in) { role = kPipeIn; idx = blockIdx.x - a.n_link; nrole = n_in; }
+  else { role = kPipeOut; idx = blockIdx.x - a.n_link - n_in; nrole = n_out; }
+
+  const uint32_t chan_off = uint32_t(c.channel) * kChannelWords;
+  auto flag_of = [&](int r, int f, int s, int writer) -> uint32_t* {
+    return c.sig[r] + chan_off + kPipeFlagBase + (f * kPipeSlots + s) * FMPI_MAX_RANKS + writer;
+  };
+  auto counter = [&](int rl, int s) -> uint32_t* { return pad + kCtlBase + kCtlPipeCnt + rl * kPipeSlots + s; };
+  // wait until flag f of slot s written by every rank in [0, W) (only_root >= 0: that rank only;
+  // skip_root >= 0: everybody but that rank) has reached `value`
+  auto wait_peers = [&](int f, int s, uint32_t value, int only, int skip) {
+    if (int(threadIdx.x) < W && (only < 0 || int(threadIdx.x) == only) && int(threadIdx.x) != skip && !x.dead)
+      x.dead = !wait_flag(flag_of(me, f, s, threadIdx.x), value, c);
+    __syncthreads();
+  };
+  auto wait_local = [&](int rl, int s, uint32_t value) {
+    if (threadIdx.x == 0 && !x.dead) x.dead = !wait_flag(counter(rl, s), value, c);
+    __syncthreads();
+  };
+  // this CTA is done with its share of the slot; the CTA that completes the count tells the peers
+  auto done = [&](int rl, int s, uint32_t total, uint32_t value) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      fence_acq_rel_sys();
+      last_s = atomicAdd(counter(rl, s), 1u) + 1 == total;
+      fence_acq_rel_sys();
+    }
+    __syncthreads();
+    if (last_s && int(threadIdx.x) < W) {
+      fence_acq_rel_sys();
+      st_release_sys(flag_of(threadIdx.x, rl, s, me), value);
+    }
+  };
+
+  const uint64_t nchunks = ceil_div(a.nvec, a.chunk_vec);
+  const uint64_t t0 = uint64_t(idx) * blockDim.x + threadIdx.x;
+  const uint64_t stride = uint64_t(nrole) * blockDim.x;
+  const uint64_t slot_bytes = a.chunk_vec * 16;
+
+  if (nrole > 0)
+    for (uint64_t k = 0; k < nchunks; ++k) {
+      const int s = int(k % S);
+      const uint32_t u = uint32_t(k / S);
+      const uint32_t U = base_s[s] + u + 1;
+      const uint64_t v0 = k * a.chunk_vec;                       // first vector of the chunk
+      const uint64_t cv = min(a.chunk_vec, a.nvec - v0);         // vectors in the chunk
+      const uint64_t per = ceil_div(cv, uint64_t(W));
+      const uint64_t soff = a.stage_off + uint64_t(s) * slot_bytes;
+
+      if (role == kPipeIn) {
+        if (u > 0) {
+          if (a.kind == 2) wait_peers(kPipeOut, s, U - 1, -1, a.root);  // receivers emptied the slot
+          else {
+            wait_peers(kPipeLink, s, U - 1, -1, -1);
+            if (n_out > 0) wait_local(kPipeOut, s, uint32_t(n_out) * u);
+          }
+        }
+        if (a.kind != 2) {
+          uint8_t* slot = byte_ptr(c.data[me], soff);
+          vec_loop<4>(0, cv, t0, stride, [&](uint64_t j) { return ld_stream(src + (v0 + j) * 16); },
+                      [&](uint64_t j, uint4 v) { *reinterpret_cast<uint4*>(slot + j * 16) = v; });
+        } else {
+          for (int dq = 0; dq < W; ++dq) {    // the root scatters: slice q -> rank q's slot
+            const int q = (me + dq) % W;
+            const uint64_t lo = min(per * q, cv), hi = min(lo + per, cv);
+            uint8_t* slot = byte_ptr(c.data[q], soff);
+            vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_stream(src + (v0 + j) * 16); },
+                        [&](uint64_t j, uint4 v) { st_stream(slot + j * 16, v); });
+          }
+        }
+        done(kPipeIn, s, uint32_t(n_in) * (u + 1), U);
+      } else if (role == kPipeLink) {
+        wait_peers(kPipeIn, s, U, a.kind == 2 ? a.root : -1, -1);
+        const uint64_t lo = min(per * me, cv), hi = min(lo + per, cv);
+        if (a.kind == 2) {
+          const uint8_t* mine = byte_ptr(c.data[me], soff);
+          if (kNvls) {
+            uint8_t* mc = byte_ptr(c.mc_data, soff);
+            vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_volatile(mine + j * 16); },
+                        [&](uint64_t j, uint4 v) { multimem_st(mc + j * 16, v); });
+          } else {
+            vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_volatile(mine + j * 16); },
+                        [&](uint64_t j, uint4 v) {
+#pragma unroll
+                          for (int r = 0; r < FMPI_MAX_RANKS; ++r)
+                            if (r < W && r != a.root && r != me) st_stream(byte_ptr(c.data[r], soff) + j * 16, v);
+                        });
+          }
+        } else if constexpr (kNvls) {
+          uint8_t* mc = byte_ptr(c.mc_data, soff);
+          uint8_t* rootslot = byte_ptr(c.data[a.kind == 1 ? a.root : me], soff);
+          vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return Multimem<T>::ld_reduce(mc + j * 16); },
+                      [&](uint64_t j, uint4 v) {
+                        if (a.kind == 0) multimem_st(mc + j * 16, v);
+                        else st_stream(rootslot + j * 16, v);
+                      });
+        } else {
+          const int dest_root = a.kind == 1 ? a.root : -1;
+          reduce_loop<T, 2, false>(
+              lo, hi, t0, stride, W, a.op, [&](int r, uint64_t j) { return byte_ptr(c.data[r], soff) + j * 16; },
+              [&](uint64_t j, uint4 v) {
+                store_to_ranks(c, dest_root, -1, [&](int r) { return byte_ptr(c.data[r], soff) + j * 16; }, v);
+              });
+        }
+        done(kPipeLink, s, uint32_t(a.n_link) * (u + 1), U);
+      } else {
+        wait_peers(kPipeLink, s, U, -1, -1);
+        const uint8_t* slot = byte_ptr(c.data[me], soff);
+        vec_loop<4>(0, cv, t0, stride, [&](uint64_t j) { return ld_volatile(slot + j * 16); },
+                    [&](uint64_t j, uint4 v) { st_stream(dst + (v0 + j) * 16, v); });
+        done(kPipeOut, s, uint32_t(n_out) * (u + 1), U);
+      }
+    }
+
+  ctx_finish(x);
+  if (last_block_done(x)) {   // every CTA of this rank is through: roll the slot bases forward
+    if (int(threadIdx.x) < S) {
+      const uint64_t uses = nchunks / S + (uint64_t(threadIdx.x) < nchunks % S ? 1 : 0);
+      pad[kCtlBase + kCtlPipeBase + threadIdx.x] = base_s[threadIdx.x] + uint32_t(uses);
+    }
+    if (threadIdx.x < 3 * kPipeSlots) pad[kCtlBase + kCtlPipeCnt + threadIdx.x] = 0;
+  }
+}
+
 __global__ void flush_l2_kernel(uint4* p, uint64_t nvec, uint32_t salt) {
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
   for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride)
@@ -484,7 +741,8 @@ struct Shape { int blocks, threads; };
 // a CTA per SM so that enough 16-byte requests are in flight to cover HBM and NVLink latency.
 Shape pick_shape(const fmpi_devcomm* c, const fmpi_launch* l, uint64_t nbytes) {
   Shape s;
-  s.threads = (l && l->threads > 0 && l->threads <= 512) ? l->threads : 512;
+  // the cross-GPU barrier signals with threads 0..world-1: never fewer than a warp, whole warps
+  s.threads = (l && l->threads > 0 && l->threads <= 512) ? ((l->threads + 31) / 32 * 32) : 512;
   if (l && l->blocks > 0) {
     s.blocks = l->blocks;
   } else {
@@ -544,6 +802,21 @@ bool want_nvls(const fmpi_devcomm* c, int algo, int dtype, int op, uint64_t nbyt
     default: rc = set_error("NVLS supports f32 / f16 / bf16 sums, got dtype %d", dt); \
   }
 
+int pipe_impl(const fmpi_devcomm* c, const void* const* in, void* const* out, uint64_t nvec, int dtype,
+              int op, int kind, int root, uint64_t stage_off, uint64_t stage_bytes, const fmpi_launch* l,
+              cudaStream_t st);
+struct PipeCfg;
+const PipeCfg& pipe_cfg();
+bool pipe_wanted(const fmpi_devcomm* c, int algo, uint64_t nbytes, int kind);
+
+// The tail of every staging region belongs to the pipelined kernels (at most a quarter of it,
+// at most 32 MB): their slots are read and written by peers outside the other families' barriers.
+uint64_t pipe_carve(uint64_t stage_bytes) {
+  uint64_t p = stage_bytes / 4;
+  if (p > (32ull << 20)) p = 32ull << 20;
+  return p & ~uint64_t(255);
+}
+
 int reduce_symm_impl(const fmpi_devcomm* c, uint64_t off, uint64_t count, int dtype, int op,
                      int dest_root, const fmpi_launch* l, cudaStream_t st) {
   if (validate(c)) return 1;
@@ -580,6 +853,17 @@ int reduce_any_impl(const fmpi_devcomm* c, const void* const* in, void* const* o
   if (count == 0) return 0;
   const uint64_t nbytes = count * es;
   const int algo = l ? l->algo : FMPI_ALGO_AUTO;
+  const int n_ranks0 = c->emulate ? c->world : 1;
+  for (int i = 0; i < n_ranks0; ++i)
+    if ((reinterpret_cast<uintptr_t>(in[i]) % 16) || (reinterpret_cast<uintptr_t>(out[i]) % 16))
+      return set_error("collective buffers must be 16-byte aligned");
+  const uint64_t pipe_bytes = pipe_carve(stage_bytes);
+  stage_bytes -= pipe_bytes;
+  if (nbytes % 16 == 0 && pipe_wanted(c, algo, nbytes, dest_root < 0 ? 0 : 1)) {
+    if (algo == FMPI_ALGO_NVLS && !nvls_capable(c, dtype, op)) return set_error("NVLS requested but not possible for this call");
+    return pipe_impl(c, in, out, nbytes / 16, dtype, op, dest_root < 0 ? 0 : 1, dest_root < 0 ? 0 : dest_root,
+                     stage_off + stage_bytes, pipe_bytes, l, st);
+  }
   // The staging area is split into private parts so that the push-without-handshake one-shot
   // kernel can never overwrite bytes a peer is still copying out of a two-shot call:
   //   [one-shot: 2 parities x W slots][two-shot: scatter W x per | result W x per]
@@ -639,12 +923,87 @@ int reduce_any_impl(const fmpi_devcomm* c, const void* const* in, void* const* o
   return rc;
 }
 
-// 0 direct, 1 scatter + all-gather, 2 multicast
-int bcast_mode(const fmpi_devcomm* c, int algo, uint64_t nbytes) {
+// ---- chunk pipeline: launch parameters (env overrides exist for the tuning runs only)
+struct PipeCfg { int link_nvls, link_p2p, copy_nvls, copy_p2p, slots; uint64_t chunk_bytes, min_ar, min_other; };
+const PipeCfg& pipe_cfg() {
+  static const PipeCfg cfg = [] {
+    auto env = [](const char* k, long d) { const char* v = getenv(k); return v && *v ? atol(v) : d; };
+    PipeCfg p;
+    p.link_nvls = int(env("FMPI_PIPE_LINK_NVLS", 16));
+    p.link_p2p = int(env("FMPI_PIPE_LINK_P2P", 64));
+    p.copy_nvls = int(env("FMPI_PIPE_COPY_NVLS", 48));
+    p.copy_p2p = int(env("FMPI_PIPE_COPY_P2P", 64));
+    p.slots = int(env("FMPI_PIPE_SLOTS", 3));
+    if (p.slots < 2) p.slots = 2;
+    if (p.slots > kPipeSlots) p.slots = kPipeSlots;
+    p.chunk_bytes = uint64_t(env("FMPI_PIPE_CHUNK_KB", 8192)) << 10;
+    p.min_ar = uint64_t(env("FMPI_PIPE_MIN_AR_KB", 48 << 10)) << 10;
+    p.min_other = uint64_t(env("FMPI_PIPE_MIN_KB", 8 << 10)) << 10;
+    return p;
+  }();
+  return cfg;
+}
+
+bool pipe_wanted(const fmpi_devcomm* c, int algo, uint64_t nbytes, int kind) {
+  if (c->world < 2) return false;
+  if (algo == FMPI_ALGO_PIPE) return true;
+  if (algo != FMPI_ALGO_AUTO) return false;
+  const PipeCfg& cfg = pipe_cfg();
+  return nbytes >= (kind == 0 ? cfg.min_ar : cfg.min_other);
+}
+
+// kind: 0 all-reduce, 1 reduce, 2 broadcast. The region [stage_off, stage_off + stage_bytes) is
+// private to the pipelined kernels of this channel (their slots are read by peers without a
+// handshake with the other kernel families).
+int pipe_impl(const fmpi_devcomm* c, const void* const* in, void* const* out, uint64_t nvec, int dtype,
+              int op, int kind, int root, uint64_t stage_off, uint64_t stage_bytes, const fmpi_launch* l,
+              cudaStream_t st) {
+  const PipeCfg& cfg = pipe_cfg();
+  const bool nvls = kind == 2 ? (c->mc_data && !c->emulate) : nvls_capable(c, dtype, op);
+  PipeArgs a{};
+  a.in = table(in, c);
+  a.out = table(reinterpret_cast<const void* const*>(out), c);
+  a.nvec = nvec; a.kind = kind; a.root = root; a.op = op; a.stage_off = stage_off;
+  a.nslots = cfg.slots;
+  uint64_t chunk = cfg.chunk_bytes;
+  if (chunk * a.nslots > stage_bytes) chunk = stage_bytes / a.nslots;
+  a.chunk_vec = chunk / 16 / c->world * c->world;
+  if (a.chunk_vec < uint64_t(c->world)) return set_error("pipeline staging area too small");
+  int total = (l && l->blocks > 0) ? l->blocks : 0;
+  if (total > 0) {
+    a.n_link = nvls ? total / 4 : total / 2;
+  } else {
+    a.n_link = nvls ? cfg.link_nvls : cfg.link_p2p;
+    total = a.n_link + (nvls ? cfg.copy_nvls : cfg.copy_p2p);
+  }
+  int cap = 144;                                   // co-resident: one CTA per SM, a few SMs spare
+  if (c->emulate) cap = 128 / c->world;
+  if (total > cap) { a.n_link = a.n_link * cap / total; total = cap; }
+  if (a.n_link < 1) a.n_link = 1;
+  if (total - a.n_link < 2) total = a.n_link + 2;
+  a.n_copy = total - a.n_link;
+  int threads = (l && l->threads > 0 && l->threads <= 512) ? (l->threads + 31) / 32 * 32 : 512;
+  int rc = 0;
+  if (nvls) {
+    FMPI_DISPATCH_NVLS(kind == 2 ? FMPI_F32 : dtype,
+                       rc = launch_ranked(pipe_kernel<T, true>, *c, total, threads, st, *c, a));
+  } else {
+    FMPI_DISPATCH_DTYPE(kind == 2 ? FMPI_U8 : dtype,
+                        rc = launch_ranked(pipe_kernel<T, false>, *c, total, threads, st, *c, a));
+  }
+  return rc;
+}
+
+// 0 direct, 1 scatter + all-gather, 2 multicast from the root, 3 pull + re-emit (symmetric only)
+int bcast_mode(const fmpi_devcomm* c, int algo, uint64_t nbytes, bool symm = false) {
   const bool mc = c->mc_data && !c->emulate;
+  if (algo == FMPI_ALGO_PIPE) return symm ? 3 : (c->world > 2 ? 1 : 0);
   if (algo == FMPI_ALGO_NVLS) return mc ? 2 : -1;
   if (algo == FMPI_ALGO_ONESHOT) return 0;
   if (algo == FMPI_ALGO_TWOSHOT) return c->world > 2 ? 1 : 0;
+  // large symmetric messages: every rank fetches its slice from the root and re-emits it, so
+  // all W links send at once (the root's multicast alone tops out near 350-390 GB/s)
+  if (symm && c->world > 2 && nbytes >= (4u << 20)) return 3;
   if (mc && c->world > 2) return 2;
   return (nbytes >= (1u << 20) && c->world > 2) ? 1 : 0;
 }
@@ -692,9 +1051,9 @@ int fmpi_bcast_symm(const fmpi_devcomm* c, uint64_t off, uint64_t nbytes, int ro
   const uint64_t nvec = (nbytes + 15) / 16;
   if (off + nvec * 16 > c->data_bytes) return set_error("region exceeds the symmetric window");
   if (nbytes == 0) return 0;
-  const int mode = bcast_mode(c, l ? l->algo : FMPI_ALGO_AUTO, nbytes);
+  const int mode = bcast_mode(c, l ? l->algo : FMPI_ALGO_AUTO, nbytes, true);
   if (mode < 0) return set_error("multicast broadcast requested but no multicast mapping");
-  const Shape s = pick_shape(c, l, nbytes);
+  const Shape s = pick_shape(c, l, mode == 3 ? nbytes / c->world : nbytes);
   return launch_ranked(bcast_symm_kernel, *c, s.blocks, s.threads, static_cast<cudaStream_t>(st),
                        *c, off, nvec, root, mode);
 }
@@ -707,6 +1066,15 @@ int fmpi_bcast_any(const fmpi_devcomm* c, void* const* buf, uint64_t nbytes, int
   if (stage_off % 16) return set_error("staging offset must be 16-byte aligned");
   if (stage_off + stage_bytes > c->data_bytes) return set_error("staging exceeds the window");
   if (nbytes == 0) return 0;
+  const uint64_t pipe_bytes = pipe_carve(stage_bytes);
+  stage_bytes -= pipe_bytes;
+  if (nbytes % 16 == 0 && pipe_wanted(c, l ? l->algo : FMPI_ALGO_AUTO, nbytes, 2)) {
+    const int n = c->emulate ? c->world : 1;
+    for (int i = 0; i < n; ++i)
+      if (reinterpret_cast<uintptr_t>(buf[i]) % 16) return set_error("bcast buffer must be 16-byte aligned");
+    return pipe_impl(c, reinterpret_cast<const void* const*>(buf), buf, nbytes / 16, FMPI_U8, FMPI_SUM, 2, root,
+                     stage_off + stage_bytes, pipe_bytes, l, static_cast<cudaStream_t>(st));
+  }
   const uint64_t half = (stage_bytes / 2) & ~uint64_t(15);
   if (half < 32) return set_error("staging area too small");
   const uint64_t chunk = half - 16;

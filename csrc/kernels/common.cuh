@@ -26,11 +26,29 @@ namespace fmpi {
 // Per channel (uint32 words):
 //   flags[FMPI_MAX_BLOCKS][FMPI_MAX_RANKS]  written by peers: flags[b][src] = src's epoch
 //   epoch[FMPI_MAX_BLOCKS]                  local: barriers block b has completed
-//   seq[FMPI_MAX_BLOCKS]                    local: push-mode calls completed (all entries
-//                                           advance together; gives a grid-independent parity)
+//   ctl[FMPI_MAX_BLOCKS]                    local control words:
+//     ctl[kCtlSeq]     push-mode calls completed on this channel (ONE word for the whole grid:
+//                      every block of a launch reads it on entry, the LAST block to finish
+//                      advances it, so no block can see the next call's parity)
+//     ctl[kCtlTicket]  blocks of the current launch that have finished (reset by the last one)
+//     ctl[kCtlPipe..]  state of the chunk-pipelined kernels (collectives.cu)
+//   pipe flags [3][kPipeSlots][FMPI_MAX_RANKS]  written by peers (pipelined kernels)
 constexpr int kFlagWords = FMPI_MAX_BLOCKS * FMPI_MAX_RANKS;
-constexpr int kChannelWords = kFlagWords + 2 * FMPI_MAX_BLOCKS;
+constexpr int kPipeSlots = 4;
+constexpr int kPipeFlagWords = 3 * kPipeSlots * FMPI_MAX_RANKS;
+constexpr int kChannelWords = kFlagWords + 2 * FMPI_MAX_BLOCKS + kPipeFlagWords;
 constexpr size_t kSigPadBytes = size_t(FMPI_NUM_CHANNELS) * kChannelWords * sizeof(uint32_t);
+constexpr int kCtlBase = kFlagWords + FMPI_MAX_BLOCKS;
+constexpr int kCtlSeq = 0, kCtlTicket = 1;
+constexpr int kCtlPipeBase = 8;                      // [kPipeSlots] slot uses in earlier calls
+constexpr int kCtlPipeCnt = kCtlPipeBase + kPipeSlots;  // [3 roles][kPipeSlots] local counters
+constexpr int kPipeFlagBase = kFlagWords + 2 * FMPI_MAX_BLOCKS;
+static_assert(kCtlPipeCnt + 3 * kPipeSlots <= FMPI_MAX_BLOCKS, "control words overflow");
+
+// Process-wide health page (pinned, mapped host memory; fmpi_devcomm::ctrl): the host sets
+// ctrl[kCtrlAbort] when it learns that a peer died, a kernel that gave up waiting sets
+// ctrl[kCtrlError]; both end every wait in flight and every later one.
+constexpr int kCtrlAbort = 0, kCtrlError = 1;
 
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
@@ -44,13 +62,48 @@ __device__ __forceinline__ void fence_acq_rel_sys() {
   asm volatile("fence.acq_rel.sys;" ::: "memory");
 }
 
+__device__ __forceinline__ uint32_t ld_relaxed_sys_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint64_t globaltimer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 struct Ctx {
   int rank;
   int world;
   uint32_t flag_off;    // word offset of this block's flags row inside a signal pad
   uint32_t* my_pad;     // this rank's signal pad, at this channel
   uint32_t epoch;
+  bool dead;            // a wait of this thread was abandoned (peer lost / abort requested)
 };
+
+// Bounded wait for *f to reach `target` (monotonic counters, wrap-safe). Returns false when the
+// wait was abandoned: the host asked for an abort, another wait already failed, or the budget
+// fmpi_devcomm::timeout_ns ran out (then the error word is set for the host to find). The
+// reference has no counterpart: a lost rank leaves its peers inside libmpi for ever.
+__device__ __forceinline__ bool wait_flag(const uint32_t* f, uint32_t target, const fmpi_devcomm& c) {
+  uint32_t spins = 0;
+  uint64_t t0 = 0;
+  while (int32_t(ld_acquire_sys(f) - target) < 0) {
+    if ((++spins & 0x3ffu) == 0 && c.ctrl) {
+      if (ld_relaxed_sys_u32(c.ctrl + kCtrlAbort) | ld_relaxed_sys_u32(c.ctrl + kCtrlError)) return false;
+      if (c.timeout_ns) {
+        const uint64_t now = globaltimer_ns();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > c.timeout_ns) {
+          atomicExch(c.ctrl + kCtrlError, 1u);
+          return false;
+        }
+      }
+    }
+  }
+  return true;
+}
 
 __device__ __forceinline__ int rank_of(const fmpi_devcomm& c) {
   return c.emulate ? int(blockIdx.y) : c.rank;
@@ -66,6 +119,7 @@ __device__ __forceinline__ void ctx_init(Ctx& x, const fmpi_devcomm& c) {
   x.flag_off = uint32_t(c.channel) * kChannelWords + blockIdx.x * FMPI_MAX_RANKS;
   x.my_pad = c.sig[x.rank] + size_t(c.channel) * kChannelWords;
   x.epoch = x.my_pad[kFlagWords + blockIdx.x];  // only this block ever writes it (at kernel end)
+  x.dead = false;
 }
 
 // Cross-GPU barrier between the same-index blocks of all ranks. Everything this block wrote
@@ -73,12 +127,10 @@ __device__ __forceinline__ void ctx_init(Ctx& x, const fmpi_devcomm& c) {
 __device__ __forceinline__ void block_barrier(Ctx& x, const fmpi_devcomm& c) {
   __syncthreads();
   const uint32_t target = ++x.epoch;
-  if (threadIdx.x < x.world) {
+  if (threadIdx.x < x.world) {   // host entry points guarantee blockDim.x >= 32 >= world
     fence_acq_rel_sys();
     st_release_sys(c.sig[threadIdx.x] + x.flag_off + x.rank, target);
-    const uint32_t* f = c.sig[x.rank] + x.flag_off + threadIdx.x;
-    while (int32_t(ld_acquire_sys(f) - target) < 0) {
-    }
+    if (!x.dead) x.dead = !wait_flag(c.sig[x.rank] + x.flag_off + threadIdx.x, target, c);
   }
   __syncthreads();
 }
@@ -87,15 +139,26 @@ __device__ __forceinline__ void ctx_finish(Ctx& x) {
   if (threadIdx.x == 0) x.my_pad[kFlagWords + blockIdx.x] = x.epoch;
 }
 
-// Push-mode call parity: identical for every block of a call whatever the grid size.
+// Push-mode call parity: one word per channel, read by every block on entry.
 __device__ __forceinline__ uint32_t seq_read(const Ctx& x) {
-  return x.my_pad[kFlagWords + FMPI_MAX_BLOCKS + blockIdx.x];
+  return ld_relaxed_sys_u32(x.my_pad + kCtlBase + kCtlSeq);
+}
+// True in exactly one block of the launch: the last one to get here (so every block of this
+// launch has already read whatever the caller is about to change). Resets the ticket.
+__device__ __forceinline__ bool last_block_done(Ctx& x) {
+  __shared__ uint32_t ticket_s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    ticket_s = atomicAdd(x.my_pad + kCtlBase + kCtlTicket, 1u);
+  }
+  __syncthreads();
+  const bool last = ticket_s == gridDim.x - 1;
+  if (last && threadIdx.x == 0) x.my_pad[kCtlBase + kCtlTicket] = 0;
+  return last;
 }
 __device__ __forceinline__ void seq_advance(Ctx& x, uint32_t cur) {
-  // all FMPI_MAX_BLOCKS counters advance on every call, split over the blocks of this grid
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < FMPI_MAX_BLOCKS;
-       i += gridDim.x * blockDim.x)
-    x.my_pad[kFlagWords + FMPI_MAX_BLOCKS + i] = cur + 1;
+  if (last_block_done(x) && threadIdx.x == 0) x.my_pad[kCtlBase + kCtlSeq] = cur + 1;
 }
 
 // ---------------------------------------------------------------------------- 16-byte vectors

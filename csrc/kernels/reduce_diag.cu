@@ -263,6 +263,7 @@ int noalloc_scratch(void** out) {
 extern "C" int fmpi_sumsq_noalloc(const void* x, uint64_t count, int dtype, double* out,
                                   fmpi_stream st) {
   if (!out) return set_error("null output");
+  if (!x && count > 0) return set_error("null input with %llu elements", (unsigned long long)count);
   if (count > FMPI_NOALLOC_MAX_COUNT)
     return set_error("fmpi_sumsq_noalloc: %llu elements exceed the limit of %llu; split the input "
                      "or use fmpi_sumsq with a caller-provided scratch buffer",

@@ -30,7 +30,7 @@ from .runtime import (Init, Initialized, Finalize, local_rank, total_workers, no
                       FluxMPINotInitializedError, host_barrier)
 from .comm import (allreduce_, bcast_, reduce_, Iallreduce, Ibcast, Request, Waitall, barrier,
                    cpu, gpu, COMM_WORLD, symm_empty, symm_zeros, is_symmetric,
-                   register_buffer, deregister_buffer, shm_empty, shm_free)
+                   shm_empty, shm_free)
 from .tree import fmap, functor
 from . import rules
 from .rules import (AbstractRule, Leaf, setup, update, update_, adjust, Descent, Momentum,

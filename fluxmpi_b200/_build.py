@@ -154,58 +154,6 @@ def _build_cuda_locked(nvcc: str, out: Path, srcs, verbose: bool) -> Path:
     return out
 
 
-def cutlass_include_dirs() -> list[Path] | None:
-    """The CUTLASS / CuTe header tree vendored with flashinfer in this image (there is no
-    /opt/cutlass); FMPI_CUTLASS_DIR overrides. None when it cannot be found."""
-    roots = []
-    if os.environ.get("FMPI_CUTLASS_DIR"):
-        roots.append(Path(os.environ["FMPI_CUTLASS_DIR"]))
-    for sp in sys.path:
-        if sp and sp.endswith("site-packages"):
-            roots.append(Path(sp) / "flashinfer" / "data" / "cutlass")
-    for r in roots:
-        inc, util = r / "include", r / "tools" / "util" / "include"
-        if (inc / "cutlass" / "cutlass.h").exists() and (util / "cutlass" / "util" / "packed_stride.hpp").exists():
-            return [inc, util]
-    return None
-
-
-GEMM_SOURCES = ["kernels/gemm_bnstats.cu"]
-
-
-def build_gemm(force: bool = False, verbose: bool = False) -> Path | None:
-    """libfmpi_gemm.so: the tcgen05 GEMM kernels written on CUTLASS templates (a separate
-    library: two minutes of template instantiation, needed only by ops/conv_bn.py). Returns
-    None when nvcc or the CUTLASS headers are missing."""
-    LIB.mkdir(exist_ok=True)
-    out = LIB / "libfmpi_gemm.so"
-    srcs = [CSRC / s for s in GEMM_SOURCES]
-    if not force and not _stale(out, srcs):           # own sources only: header edits elsewhere
-        return out                                    # must not cost a CUTLASS rebuild
-    nvcc, inc = _nvcc(), cutlass_include_dirs()
-    if nvcc is None or inc is None:
-        return out if out.exists() else None
-    with _BuildLock():
-        if not force and not _stale(out, srcs):
-            return out
-        tmp = out.with_suffix(f".so.tmp{os.getpid()}")
-        cmd = [nvcc, "-O3", "-std=c++17", *NVCC_ARCH, "-lineinfo", "--expt-relaxed-constexpr", "-shared",
-               "-Xcompiler", "-fPIC", *[f"-I{d}" for d in inc], f"-I{INC}", *map(str, srcs), "-o", str(tmp),
-               "-cudart", "static", "-lpthread", "-ldl", "-lrt"]
-        # CUTLASS's workspace fill calls the driver API directly (cuMemsetD32Async): record
-        # libcuda.so.1 as a dependency through the toolkit's link-time stub, so the library
-        # resolves on a GPU box (and simply cannot be loaded on a machine without a driver)
-        stubs = Path(nvcc).resolve().parent.parent / "lib64" / "stubs"
-        if (stubs / "libcuda.so").exists():
-            cmd += [f"-L{stubs}", "-lcuda"]
-        if verbose:
-            print(" ".join(cmd), file=sys.stderr)
-        subprocess.run(cmd, check=True)
-        os.replace(tmp, out)
-        _mark(out, srcs)
-    return out
-
-
 def build_all(force: bool = False, verbose: bool = False):
     return build_host(force, verbose), build_cuda(force, verbose)
 
@@ -214,4 +162,3 @@ if __name__ == "__main__":
     h, c = build_all(force="--force" in sys.argv, verbose=True)
     print("host:", h)
     print("cuda:", c)
-    print("gemm:", build_gemm(force="--force" in sys.argv, verbose=True))

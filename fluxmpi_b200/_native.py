@@ -20,7 +20,7 @@ NUM_CHANNELS = 4
 F32, F64, F16, BF16, I32, I64, U8, I8, I16 = range(9)
 SUM, PROD, MIN, MAX = range(4)
 RULE_DESCENT, RULE_MOMENTUM, RULE_NESTEROV, RULE_ADAM, RULE_ADAMW = range(5)
-ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = range(4)
+ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS, ALGO_PIPE = range(5)
 SYMM_VMM, SYMM_IPC, SYMM_LOCAL = range(3)
 
 OPS = {"sum": SUM, "+": SUM, "add": SUM, "prod": PROD, "*": PROD, "mul": PROD,
@@ -134,6 +134,8 @@ class DevComm(C.Structure):
         ("sig", C.c_void_p * MAX_RANKS),
         ("mc_data", C.c_void_p),
         ("data_bytes", C.c_uint64),
+        ("ctrl", C.c_void_p),
+        ("timeout_ns", C.c_uint64),
     ]
 
 
@@ -201,6 +203,7 @@ def cuda():
         lib.fmpi_symm_mc_ptr.restype = vp
         lib.fmpi_symm_destroy.argtypes = [vp]
         lib.fmpi_sigpad_bytes.restype = C.c_size_t
+        lib.fmpi_health_page.argtypes = [C.POINTER(vp), C.POINTER(vp)]
         dc, lp = C.POINTER(DevComm), C.POINTER(Launch)
         lib.fmpi_allreduce_symm.argtypes = [dc, u64, u64, i32, i32, lp, vp]
         lib.fmpi_bcast_symm.argtypes = [dc, u64, u64, i32, lp, vp]
@@ -211,6 +214,8 @@ def cuda():
         lib.fmpi_barrier_dev.argtypes = [dc, vp]
         lib.fmpi_fused_step.argtypes = [dc, u64, i32, u64, i32, vp, vp, vp, u64, u64,
                                         C.POINTER(Hyper), vp, lp, vp]
+        lib.fmpi_fused_step_oneshot.argtypes = [dc, u64, u64, i32, vp, vp, vp, u64, u64,
+                                                C.POINTER(Hyper), vp, u64, u64, lp, vp]
         lib.fmpi_step_advance.argtypes = [vp, vp]
         lib.fmpi_multi_tensor_step.argtypes = [i32, vp, vp, vp, vp, vp, i32, i32,
                                                C.POINTER(Hyper), C.c_int64, vp]
@@ -224,7 +229,6 @@ def cuda():
         lib.fmpi_bn_scratch_bytes.argtypes = [i32]
         lib.fmpi_bn_scratch_bytes.restype = C.c_size_t
         lib.fmpi_bn_forward.argtypes = [vp, vp, vp, u64, i32, i32, vp, vp, vp, vp, f32, f32, i32, vp, vp, vp, vp]
-        lib.fmpi_bn_forward_presummed.argtypes = list(lib.fmpi_bn_forward.argtypes)
         lib.fmpi_bn_apply.argtypes = [vp, vp, vp, u64, i32, i32, vp, vp, i32, vp]
         lib.fmpi_bn_backward.argtypes = [vp, vp, vp, vp, vp, u64, i32, i32, vp, vp, vp, vp, vp, i32, vp, vp]
         lib.fmpi_maxpool_fwd.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]

@@ -452,28 +452,6 @@ def symm_empty(shape, dtype=torch.float32):
     return dw.symm_empty(shape, dtype)
 
 
-def register_buffer(t: torch.Tensor):
-    """EXPERIMENTAL (not yet run on GPUs). Collective: map this rank's CUDA tensor into every
-    peer through CUDA IPC so collectives on it run in place over NVLink like on ``symm_empty``
-    tensors (what NCCL calls user-buffer registration). Every rank passes a contiguous tensor of
-    the same byte size. Returns a handle for :func:`deregister_buffer`, or None when the world
-    has no peer mappings or the mapping failed (the tensor then keeps the staged path). Call
-    ``deregister_buffer`` before ``torch.cuda.empty_cache()`` or before the tensor is freed."""
-    if not runtime.Initialized():
-        raise runtime.FluxMPINotInitializedError()
-    dw = runtime.state().device_world
-    if dw is None or not dw.native or not isinstance(t, torch.Tensor) or not t.is_cuda:
-        return None
-    return dw.register_buffer(t)
-
-
-def deregister_buffer(handle) -> None:
-    """Collective counterpart of :func:`register_buffer` (a None handle is a no-op)."""
-    dw = runtime.state().device_world
-    if handle is not None and dw is not None:
-        dw.deregister_buffer(handle)
-
-
 def symm_zeros(shape, dtype=torch.float32):
     t = symm_empty(shape, dtype)
     t.zero_()

@@ -83,8 +83,6 @@ def main(argv=None) -> int:
     rep.add("ok" if shutil.which("g++") else "FAIL", "g++ (host library)", shutil.which("g++") or "not found")
     nvcc = _build._nvcc()
     rep.add("ok" if nvcc else "warn", "nvcc (CUDA library)", nvcc or "not found: prebuilt libraries only")
-    cut = _build.cutlass_include_dirs()
-    rep.add("ok" if cut else "warn", "CUTLASS headers (experimental GEMM library)", str(cut[0]) if cut else "not found")
     try:
         rep.add("ok", "libfmpi_host.so", str(_build.build_host()))
     except Exception as e:                                       # noqa: BLE001

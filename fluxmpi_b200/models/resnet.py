@@ -15,7 +15,6 @@ import torch
 from torch import nn
 
 from ..ops.batchnorm import FusedBatchNormAct
-from ..ops.conv_bn import conv1x1_bn_act, enabled_by_env
 from ..ops.pool import FusedMaxPool2d
 
 
@@ -27,10 +26,9 @@ class Bottleneck(nn.Module):
     expansion = 4
 
     def __init__(self, inplanes: int, planes: int, stride: int = 1, downsample: nn.Module | None = None,
-                 fused_bn: bool = False, fused_conv_bn: bool = False):
+                 fused_bn: bool = False):
         super().__init__()
         self.fused_bn = fused_bn
-        self.fused_conv_bn = fused_bn and fused_conv_bn
         self.conv1 = nn.Conv2d(inplanes, planes, 1, bias=False)
         self.bn1 = _bn(planes, True, fused_bn)
         self.conv2 = nn.Conv2d(planes, planes, 3, stride=stride, padding=1, bias=False)
@@ -41,14 +39,6 @@ class Bottleneck(nn.Module):
         self.downsample = downsample
 
     def forward(self, x):
-        if self.fused_conv_bn:
-            # experimental: 1x1 convolutions as tcgen05 GEMMs that also take the BatchNorm
-            # statistics (ops/conv_bn.py); anything that does not qualify (the strided
-            # downsample convolutions, eval mode, ...) takes bn(conv(x)) inside the helper
-            identity = x if self.downsample is None else conv1x1_bn_act(x, self.downsample[0], self.downsample[1])
-            out = conv1x1_bn_act(x, self.conv1, self.bn1)
-            out = self.bn2(self.conv2(out))
-            return conv1x1_bn_act(out, self.conv3, self.bn3, identity)
         identity = x if self.downsample is None else self.downsample(x)
         if self.fused_bn:
             out = self.bn1(self.conv1(x))                       # bn + relu in one pass
@@ -61,11 +51,9 @@ class Bottleneck(nn.Module):
 
 
 class ResNet(nn.Module):
-    def __init__(self, layers=(3, 4, 6, 3), num_classes: int = 1000, width: int = 64, fused_bn: bool = False,
-                 fused_conv_bn: bool | None = None):
+    def __init__(self, layers=(3, 4, 6, 3), num_classes: int = 1000, width: int = 64, fused_bn: bool = False):
         super().__init__()
         self.fused_bn = fused_bn
-        self.fused_conv_bn = fused_bn and (enabled_by_env() if fused_conv_bn is None else fused_conv_bn)
         self.inplanes = width
         self.conv1 = nn.Conv2d(3, width, 7, stride=2, padding=3, bias=False)
         self.bn1 = _bn(width, True, fused_bn)
@@ -90,9 +78,9 @@ class ResNet(nn.Module):
             downsample = nn.Sequential(
                 nn.Conv2d(self.inplanes, planes * Bottleneck.expansion, 1, stride=stride, bias=False),
                 _bn(planes * Bottleneck.expansion, False, self.fused_bn))
-        layers = [Bottleneck(self.inplanes, planes, stride, downsample, self.fused_bn, self.fused_conv_bn)]
+        layers = [Bottleneck(self.inplanes, planes, stride, downsample, self.fused_bn)]
         self.inplanes = planes * Bottleneck.expansion
-        layers += [Bottleneck(self.inplanes, planes, fused_bn=self.fused_bn, fused_conv_bn=self.fused_conv_bn)
+        layers += [Bottleneck(self.inplanes, planes, fused_bn=self.fused_bn)
                    for _ in range(1, blocks)]
         return nn.Sequential(*layers)
 
@@ -105,10 +93,10 @@ class ResNet(nn.Module):
         return self.fc(torch.flatten(self.avgpool(x), 1))
 
 
-def resnet50(num_classes: int = 1000, fused_bn: bool = False, fused_conv_bn: bool | None = None) -> ResNet:
-    return ResNet((3, 4, 6, 3), num_classes, fused_bn=fused_bn, fused_conv_bn=fused_conv_bn)
+def resnet50(num_classes: int = 1000, fused_bn: bool = False) -> ResNet:
+    return ResNet((3, 4, 6, 3), num_classes, fused_bn=fused_bn)
 
 
-def resnet_tiny(num_classes: int = 10, fused_bn: bool = False, fused_conv_bn: bool | None = None) -> ResNet:
+def resnet_tiny(num_classes: int = 10, fused_bn: bool = False) -> ResNet:
     """Same topology, 1 block per stage, width 16 — for smoke tests."""
-    return ResNet((1, 1, 1, 1), num_classes, width=16, fused_bn=fused_bn, fused_conv_bn=fused_conv_bn)
+    return ResNet((1, 1, 1, 1), num_classes, width=16, fused_bn=fused_bn)

@@ -94,12 +94,17 @@ class _Base:
             c.sig[r] = sig_ptrs[r]
         c.mc_data = mc_ptr or None
         c.data_bytes = data_bytes
+        c.ctrl = getattr(self, "_ctrl_dev", 0) or None      # health page (real worlds only)
+        c.timeout_ns = int(getattr(self, "_timeout_ns", 0))
         return c
 
 
 class DeviceWorld(_Base):
-    AR_STAGE_MB = int(os.environ.get("FMPI_AR_STAGE_MB", 160))
-    BCAST_STAGE_MB = int(os.environ.get("FMPI_BCAST_STAGE_MB", 64))
+    # staging per signal channel: 0 = blocking collectives, 1 = non-blocking ones (their kernels
+    # may overlap, so they must not share slots); the engine's channel 2 needs no staging
+    AR_STAGE_MB = (int(os.environ.get("FMPI_AR_STAGE_MB", 160)), int(os.environ.get("FMPI_AR_ASYNC_STAGE_MB", 64)))
+    BCAST_STAGE_MB = (int(os.environ.get("FMPI_BCAST_STAGE_MB", 96)), int(os.environ.get("FMPI_BCAST_ASYNC_STAGE_MB", 32)))
+    MAX_COMMS = 8            # signal-pad sets: 0 = the world, 1.. = rank groups (fm.Group)
 
     def __init__(self, rank: int, world: int, device: int, job: str):
         self.rank, self.world = rank, world
@@ -120,8 +125,11 @@ class DeviceWorld(_Base):
         self._heap = None                 # [segment, bump offset] for symm_empty
         self._symm_regs: list = []        # registered symmetric segments (user-visible tensors)
         self.tuner = None
-        self._pipe = None                 # (arena slots, streams) of the chunk pipeline
         self._pack_arena = None           # symmetric target of tree-level pack kernels
+        self._ctrl_host = None            # health page (host view) of this process's device
+        self._ctrl_dev = 0
+        self._timeout_ns = 0
+        self._groups: dict = {}           # comm id -> Group state
 
     # ------------------------------------------------------------------ bring-up
     def _topology(self):
@@ -275,11 +283,26 @@ class DeviceWorld(_Base):
     def bring_up(self, disabled: bool, verbose: bool):
         lib = _native.cuda()      # raises if the library is missing: no silent fallback
         self._topology()
-        self.sig_bytes = _align(lib.fmpi_sigpad_bytes(), 1 << 16)
-        self.ar_off = 0
-        self.ar_bytes = self.AR_STAGE_MB * MB
-        self.bc_off = self.ar_bytes
-        self.bc_bytes = self.BCAST_STAGE_MB * MB
+        self.pad_bytes = _align(lib.fmpi_sigpad_bytes(), 1 << 16)      # one set of signal pads
+        self.sig_bytes = self.pad_bytes * self.MAX_COMMS                # all sets, then the data window
+        off = 0
+        self.ar_regions, self.bc_regions = [], []
+        for mb in self.AR_STAGE_MB:
+            self.ar_regions.append((off, mb * MB))
+            off += mb * MB
+        for mb in self.BCAST_STAGE_MB:
+            self.bc_regions.append((off, mb * MB))
+            off += mb * MB
+        self._window_bytes = off
+        self.ar_off, self.ar_bytes = self.ar_regions[0]
+        self.bc_off, self.bc_bytes = self.bc_regions[0]
+        # health page: lets a kernel give up on a lost peer and lets the host stop the kernels
+        hp, dp = C.c_void_p(), C.c_void_p()
+        cuda_check(lib.fmpi_health_page(C.byref(hp), C.byref(dp)), "health page")
+        self._ctrl_host = (C.c_uint32 * 16).from_address(hp.value)
+        self._ctrl_dev = dp.value
+        from .. import runtime as _rt
+        self._timeout_ns = int(float(os.environ.get("FMPI_DEVICE_TIMEOUT_S", _rt.state().timeout_s)) * 1e9)
         self.comm_stream = torch.cuda.Stream(self.device, priority=-1)
         if disabled and self.world > 1:
             self.why_fallback = "P2P support disabled by preference"
@@ -294,10 +317,13 @@ class DeviceWorld(_Base):
             self.why_fallback = f"the job spans {self.nnodes} nodes and the NVLink kernels are node-local"
             return
         try:
-            need = self.sig_bytes + self.ar_bytes + self.bc_bytes
+            need = self.sig_bytes + self._window_bytes
             if self.world == 1:
                 need = self.sig_bytes + 4 * MB
-                self.ar_bytes, self.bc_off, self.bc_bytes = 2 * MB, 2 * MB, 2 * MB
+                self.ar_regions = [(0, MB), (MB, MB)]
+                self.bc_regions = [(2 * MB, MB), (3 * MB, MB)]
+                self.ar_off, self.ar_bytes = self.ar_regions[0]
+                self.bc_off, self.bc_bytes = self.bc_regions[0]
             self.base = self.alloc_segment(need)
         except _native.NativeError as e:
             if self.world > 1 and os.environ.get("FMPI_REQUIRE_P2P", "0") not in ("0", ""):
@@ -322,14 +348,40 @@ class DeviceWorld(_Base):
         self._in1_ref, self._out1_ref = C.byref(self._in1), C.byref(self._out1)
 
     def comm_for(self, seg: Segment, channel: int, data_offset: int = 0,
-                 data_bytes: Optional[int] = None) -> DevComm:
-        """Device communicator over ``seg`` (signal pads always come from the base segment)."""
+                 data_bytes: Optional[int] = None, comm_id: int = 0, members=None) -> DevComm:
+        """Device communicator over ``seg`` (signal pads always come from the base segment; set
+        ``comm_id`` of them). ``members`` (world ranks, ascending) restricts it to a rank group:
+        the tables then hold only the members' pointers and ranks are group ranks."""
         base = self.base if self.base is not None else seg
-        data = [p + data_offset for p in seg.peer_ptrs]
-        sig = list(base.peer_ptrs)
-        mc = seg.mc_ptr + data_offset if seg.mc_ptr else 0
+        members = list(range(self.world)) if members is None else list(members)
+        data = [seg.peer_ptrs[r] + data_offset for r in members]
+        sig = [base.peer_ptrs[r] + comm_id * self.pad_bytes for r in members]
+        whole = len(members) == self.world
+        mc = seg.mc_ptr + data_offset if (seg.mc_ptr and whole) else 0   # the multicast object spans the world
         nbytes = (seg.size - data_offset) if data_bytes is None else data_bytes
-        return self._mk_comm(data, sig, nbytes, channel, self.rank, 0, mc)
+        c = DevComm()
+        c.rank, c.world, c.emulate, c.channel = members.index(self.rank), len(members), 0, channel
+        for i in range(len(members)):
+            c.data[i] = data[i]
+            c.sig[i] = sig[i]
+        c.mc_data = mc or None
+        c.data_bytes = nbytes
+        c.ctrl = self._ctrl_dev or None
+        c.timeout_ns = self._timeout_ns
+        return c
+
+    def check_health(self):
+        """Raise if a kernel gave up waiting for a peer (or the world was aborted)."""
+        h = self._ctrl_host
+        if h is not None and (h[0] or h[1]):
+            rc = self._lib.fmpi_health_check() if hasattr(self, "_lib") else _native.cuda().fmpi_health_check()
+            cuda_check(rc or 1, "device world")
+
+    def abort(self):
+        """Make every cross-GPU wait on this GPU return (called when the host world reports a
+        dead peer): the kernels in flight finish at once with undefined results."""
+        if self._ctrl_host is not None:
+            self._ctrl_host[0] = 1
 
     # ------------------------------------------------------------------ NCCL fallback
     def _nccl(self):
@@ -384,16 +436,17 @@ class DeviceWorld(_Base):
             lp = tl[0] if tl else self._lp_auto
         i, o = self._in1, self._out1     # reusable one-entry pointer tables (read at launch)
         sp, dp = src.data_ptr(), dst.data_ptr()
+        ar_off, ar_bytes = self.ar_regions[1 if channel == 1 else 0]
         off = 0
         for cnt in ((bulk, n - bulk) if bulk < n else (bulk,)):
             if cnt:
                 i.value, o.value = sp + off * es, dp + off * es
                 if root < 0:
                     rc = lib.fmpi_allreduce_any(comm, self._in1_ref, self._out1_ref, cnt, code, op,
-                                                self.ar_off, self.ar_bytes, lp, st)
+                                                ar_off, ar_bytes, lp, st)
                 else:
                     rc = lib.fmpi_reduce_any(comm, self._in1_ref, self._out1_ref, cnt, code, op, root,
-                                             self.ar_off, self.ar_bytes, lp, st)
+                                             ar_off, ar_bytes, lp, st)
                 if rc:
                     cuda_check(rc, "allreduce" if root < 0 else "reduce")
                 _native.launch_count += 1
@@ -427,106 +480,12 @@ class DeviceWorld(_Base):
 
     def find_symmetric(self, t: torch.Tensor):
         """(comm refs, byte offset, has multicast) if ``t`` lives in a registered symmetric
-        segment or in a user buffer registered with :meth:`register_buffer`."""
+        segment."""
         p = t.data_ptr()
         for lo, hi, seg, comms, refs in self._symm_regs:
             if lo <= p < hi and p + t.numel() * t.element_size() <= hi:
                 return refs, p - lo, bool(comms[0].mc_data)
         return None
-
-    # ------------------------------------------------------------------ user buffers (CUDA IPC)
-    # EXPERIMENTAL (written without GPU time, not yet run): what NCCL calls user-buffer
-    # registration. A tensor from the ordinary allocator is mapped into every peer through the
-    # CUDA-IPC handle of the cudaMalloc block that holds it; collectives on it then use the
-    # in-place peer-to-peer kernels (no staging copies, no multicast) like symm_empty tensors.
-    def register_buffer(self, t: torch.Tensor):
-        """Collective: every rank passes its own contiguous CUDA tensor of the same byte size.
-        Returns a registration object (or None when any rank could not export / map; the
-        tensor then keeps taking the staged path). The mapping is valid while the allocation
-        lives: call :meth:`deregister_buffer` before ``torch.cuda.empty_cache()``."""
-        import struct
-        from .. import runtime
-        if not (self.native and self.world > 1):
-            return None
-        from cuda.bindings import driver as drv, runtime as rt
-        W, r = self.world, self.rank
-        nbytes = t.numel() * t.element_size()
-        ok = t.is_cuda and t.is_contiguous() and t.data_ptr() % 16 == 0 and nbytes > 0 and nbytes % 16 == 0
-        handle, off = bytes(64), 0
-        if ok:
-            err, base, _size = drv.cuMemGetAddressRange(t.data_ptr())
-            ok = int(err) == 0
-            if ok:
-                err, h = rt.cudaIpcGetMemHandle(int(base))
-                ok = int(err) == 0
-                if ok:
-                    handle, off = bytes(h.reserved), t.data_ptr() - int(base)
-        blobs = runtime.host_allgather_bytes(handle + struct.pack("<QQQ", off, nbytes, int(ok)), 88)
-        metas = [(b[:64],) + struct.unpack("<QQQ", b[64:88]) for b in blobs]
-        good = all(m[3] == 1 and m[2] == nbytes for m in metas)
-        ptrs, opened = [0] * W, []
-        if good:
-            for q, (hq, offq, _n, _f) in enumerate(metas):
-                if q == r:
-                    ptrs[q] = t.data_ptr()
-                    continue
-                base_q = self._ipc_open(q, hq)
-                if base_q is None:
-                    good = False
-                    break
-                opened.append((q, hq))
-                ptrs[q] = base_q + offq
-        if not self._all_agree(good):
-            for q, hq in opened:
-                self._ipc_release(q, hq)
-            warnings.warn("[fluxmpi_b200] register_buffer: CUDA-IPC export or mapping failed on some rank; "
-                          "the tensor stays on the staged path")
-            return None
-        comms = [self._mk_comm(ptrs, list(self.base.peer_ptrs), nbytes, ch, r, 0, 0)
-                 for ch in range(_native.NUM_CHANNELS)]
-        entry = (t.data_ptr(), t.data_ptr() + nbytes, ("ipc", opened, t), comms, [C.byref(c) for c in comms])
-        self._symm_regs.append(entry)
-        runtime.host_barrier()
-        return entry
-
-    def deregister_buffer(self, entry) -> None:
-        """Collective. Unmaps the peers' views; later collectives on the tensor are staged."""
-        from .. import runtime
-        if entry is None:
-            return
-        torch.cuda.synchronize(self.device)
-        runtime.host_barrier()                       # nobody is still reading this rank's block
-        if entry in self._symm_regs:
-            self._symm_regs.remove(entry)
-        for q, hq in entry[2][1]:
-            self._ipc_release(q, hq)
-        runtime.host_barrier()
-
-    def _ipc_open(self, q: int, handle: bytes):
-        from cuda.bindings import runtime as rt
-        cache = self.__dict__.setdefault("_ipc_cache", {})
-        hit = cache.get((q, handle))
-        if hit is not None:
-            hit[1] += 1
-            return hit[0]
-        h = rt.cudaIpcMemHandle_t()
-        h.reserved = handle
-        err, ptr = rt.cudaIpcOpenMemHandle(h, rt.cudaIpcMemLazyEnablePeerAccess)
-        if int(err) != 0:
-            return None
-        cache[(q, handle)] = [int(ptr), 1]
-        return int(ptr)
-
-    def _ipc_release(self, q: int, handle: bytes):
-        from cuda.bindings import runtime as rt
-        cache = self.__dict__.get("_ipc_cache", {})
-        hit = cache.get((q, handle))
-        if hit is None:
-            return
-        hit[1] -= 1
-        if hit[1] <= 0:
-            rt.cudaIpcCloseMemHandle(hit[0])
-            del cache[(q, handle)]
 
     def _symm_collective(self, kind: str, t: torch.Tensor, hit, op: int, root: int, channel: int, stream):
         refs, off, has_mc = hit
@@ -535,7 +494,7 @@ class DeviceWorld(_Base):
         st = (torch.cuda.current_stream() if stream is None else stream).cuda_stream
         tl = self.tuner.launch("bcast_symm" if kind == "bcast" else "allreduce_symm", nbytes)
         if tl and tl[1].algo == _native.ALGO_NVLS and not has_mc:
-            tl = None       # a registered user buffer has no multicast alias: peer-to-peer kernels
+            tl = None       # no multicast alias on this segment: peer-to-peer kernels
         if tl and kind != "bcast" and tl[1].algo == _native.ALGO_NVLS and not (
                 op == _native.SUM and t.dtype in (torch.float32, torch.bfloat16, torch.float16)):
             tl = None       # the switch only adds f32/f16/bf16: other ops/dtypes take the P2P kernel
@@ -550,74 +509,6 @@ class DeviceWorld(_Base):
             cuda_check(rc, kind)
         _native.launch_count += 1
 
-    # ------------------------------------------------------------------ large arbitrary buffers
-    # A big tensor that is NOT in symmetric memory is moved through a two-slot symmetric arena
-    # in chunks: copy-in (copy stream) -> in-place NVLink kernel on the slot (comm stream,
-    # 8-16 CTAs) -> copy-out (third stream). The three stages of consecutive chunks overlap, so
-    # the cost of staging hides behind the link time instead of adding to it (measured at 8
-    # GPUs, 1 GiB: in-place symmetric all-reduce 837 GB/s bus bandwidth vs 510 GB/s for the
-    # single-kernel staged path).
-    # Off by default (0): measured at 4 GPUs the per-chunk kernel overheads eat the overlap
-    # (256 MB: 860 us pipelined vs 833 us single staged kernel vs 645 us in place on symmetric
-    # memory). Set FMPI_PIPELINE_MIN_MB to opt in; fm.symm_empty is the real fix.
-    PIPE_MIN_BYTES = int(float(os.environ.get("FMPI_PIPELINE_MIN_MB", 0)) * MB)
-    PIPE_CHUNK_BYTES = int(float(os.environ.get("FMPI_PIPELINE_CHUNK_MB", 32)) * MB)
-
-    def _pipe_setup(self):
-        if self._pipe is None:
-            slots = [self.symm_empty((self.PIPE_CHUNK_BYTES,), torch.uint8) for _ in range(2)]
-            streams = [torch.cuda.Stream(self.device, priority=-1) for _ in range(3)]
-            self._pipe = (slots, streams)
-        return self._pipe
-
-    def _pipelined(self, kind: str, t: torch.Tensor, op: int, root: int):
-        slots, (s_in, s_comm, s_out) = self._pipe_setup()
-        cur = torch.cuda.current_stream()
-        es = t.element_size()
-        flat = t.view(-1)
-        n = flat.numel()
-        chunk = self.PIPE_CHUNK_BYTES // es
-        for s in (s_in, s_comm, s_out):
-            s.wait_stream(cur)
-        free_ev = [None, None]
-        sends = kind != "bcast" or self.rank == root
-        recvs = kind == "allreduce" or (kind == "bcast" and self.rank != root) or \
-            (kind == "reduce" and self.rank == root)
-        for k, lo in enumerate(range(0, n, chunk)):
-            hi = min(lo + chunk, n)
-            slot = slots[k % 2]
-            cnt = hi - lo
-            padded = (cnt * es + 15) // 16 * 16 // es
-            a = slot[:padded * es].view(t.dtype)
-            with torch.cuda.stream(s_in):
-                if free_ev[k % 2] is not None:
-                    s_in.wait_event(free_ev[k % 2])
-                if sends:
-                    a[:cnt].copy_(flat[lo:hi], non_blocking=True)
-                ev_in = torch.cuda.Event()
-                ev_in.record(s_in)
-            with torch.cuda.stream(s_comm):
-                s_comm.wait_event(ev_in)
-                self._symm_collective(kind, a, self.find_symmetric(a), op, root, 3, s_comm)
-                ev_c = torch.cuda.Event()
-                ev_c.record(s_comm)
-            with torch.cuda.stream(s_out):
-                s_out.wait_event(ev_c)
-                if recvs:
-                    flat[lo:hi].copy_(a[:cnt], non_blocking=True)
-                ev_o = torch.cuda.Event()
-                ev_o.record(s_out)
-            free_ev[k % 2] = ev_o
-        for s in (s_in, s_comm, s_out):
-            cur.wait_stream(s)
-        t.record_stream(s_in)
-        t.record_stream(s_out)
-
-    def _pipe_ok(self, t: torch.Tensor) -> bool:
-        return (self.PIPE_MIN_BYTES > 0 and self.native and self.world > 1 and t.is_contiguous()
-                and t.dtype != torch.bool and t.numel() * t.element_size() >= self.PIPE_MIN_BYTES
-                and self.PIPE_CHUNK_BYTES > 0)
-
     def _symm_hit(self, t: torch.Tensor):
         if not self._symm_regs or not t.is_contiguous() or t.dtype == torch.bool:
             return None
@@ -629,13 +520,12 @@ class DeviceWorld(_Base):
     def allreduce(self, t: torch.Tensor, op: int, launch=None):
         if self.world == 1 or t.numel() == 0:
             return t
+        if self.native:
+            self.check_health()
         if self.native and launch is None:
             hit = self._symm_hit(t)
             if hit is not None:
                 self._symm_collective("allreduce", t.detach() if t.requires_grad else t, hit, op, -1, 0, None)
-                return t
-            if self._pipe_ok(t):
-                self._pipelined("allreduce", t.detach() if t.requires_grad else t, op, -1)
                 return t
         w, copy = self._work_tensor(t)
         if self.native:
@@ -653,9 +543,6 @@ class DeviceWorld(_Base):
             hit = self._symm_hit(t)
             if hit is not None:
                 self._symm_collective("reduce", t.detach() if t.requires_grad else t, hit, op, root, 0, None)
-                return t
-            if self._pipe_ok(t):
-                self._pipelined("reduce", t.detach() if t.requires_grad else t, op, root)
                 return t
         w, copy = self._work_tensor(t)
         if self.native:
@@ -677,17 +564,15 @@ class DeviceWorld(_Base):
             if hit is not None:
                 self._symm_collective("bcast", t.detach() if t.requires_grad else t, hit, 0, root, channel, stream)
                 return t
-            if stream is None and self._pipe_ok(t):
-                self._pipelined("bcast", t.detach() if t.requires_grad else t, 0, root)
-                return t
         w, copy = self._work_tensor(t)
         if self.native:
             lib = self._lib
             nbytes = w.numel() * w.element_size()
             tl = self.tuner.launch("bcast_any", nbytes)
             self._in1.value = w.data_ptr()
-            rc = lib.fmpi_bcast_any(self._comm_refs[channel], self._in1_ref, nbytes, root, self.bc_off,
-                                    self.bc_bytes, tl[0] if tl else self._lp_auto,
+            bc_off, bc_bytes = self.bc_regions[1 if channel == 1 else 0]
+            rc = lib.fmpi_bcast_any(self._comm_refs[channel], self._in1_ref, nbytes, root, bc_off,
+                                    bc_bytes, tl[0] if tl else self._lp_auto,
                                     (torch.cuda.current_stream() if stream is None else stream).cuda_stream)
             if rc:
                 cuda_check(rc, "bcast")
@@ -810,6 +695,7 @@ class DeviceWorld(_Base):
 
     def barrier(self, stream=None):
         if self.world > 1 and self.native:
+            self.check_health()
             cuda_check(_native.cuda().fmpi_barrier_dev(C.byref(self.comms[0]), _stream_ptr(stream)), "barrier")
             _native.count_launch()
 
@@ -856,6 +742,13 @@ class EmulatedWorld(_Base):
         if self.device.index is None:
             self.device = torch.device("cuda", torch.cuda.current_device())
         self.sig_bytes = _align(lib.fmpi_sigpad_bytes(), 1 << 16)
+        # bounded waits here too: a protocol bug ends in an error, not in a kernel that spins
+        hp, dp = C.c_void_p(), C.c_void_p()
+        with torch.cuda.device(self.device):
+            cuda_check(lib.fmpi_health_page(C.byref(hp), C.byref(dp)), "health page")
+        self._ctrl_host = (C.c_uint32 * 16).from_address(hp.value)
+        self._ctrl_dev = dp.value
+        self._timeout_ns = int(float(os.environ.get("FMPI_DEVICE_TIMEOUT_S", 20)) * 1e9)
         self.ar_off, self.ar_bytes = 0, stage_mb * MB
         self.bc_off, self.bc_bytes = self.ar_bytes, stage_mb * MB
         self.heap_off = self.bc_off + self.bc_bytes
@@ -867,6 +760,10 @@ class EmulatedWorld(_Base):
         self.comms = [self._mk_comm([b + self.sig_bytes for b in base], base, self.window_bytes, ch, 0, 1)
                       for ch in range(_native.NUM_CHANNELS)]
         self._heap_top = self.heap_off
+
+    def check_health(self):
+        if self._ctrl_host[0] or self._ctrl_host[1]:
+            cuda_check(_native.cuda().fmpi_health_check() or 1, "emulated world")
 
     # window helpers ------------------------------------------------------------------
     def window(self, rank: int, offset: int, nbytes: int) -> torch.Tensor:
@@ -941,4 +838,16 @@ class EmulatedWorld(_Base):
         cuda_check(lib.fmpi_fused_step(C.byref(self.comms[channel]), g_off, code, p_off, code, arr(m),
                                        arr(v), arr(master), lo, hi, C.byref(hyper), arr(step_dev),
                                        self._launch(blocks), _stream_ptr()), "emulated fused_step")
+        _native.count_launch()
+
+    def fused_step_oneshot(self, g_off: int, p_off: int, dtype: torch.dtype, m, v, master, lo: int, hi: int,
+                           hyper, step_dev, stage_off: int, stage_bytes: int, blocks: int = 0, channel: int = 2):
+        """One-shot flavour (push to every peer, one barrier, every rank applies the whole rule)."""
+        lib = _native.cuda()
+        code = _dtype_code(dtype)
+        arr = lambda ts: self._ptrs(ts) if ts is not None else None
+        cuda_check(lib.fmpi_fused_step_oneshot(C.byref(self.comms[channel]), g_off, p_off, code, arr(m), arr(v),
+                                               arr(master), lo, hi, C.byref(hyper), arr(step_dev), stage_off,
+                                               stage_bytes, self._launch(blocks), _stream_ptr()),
+                   "emulated fused_step_oneshot")
         _native.count_launch()

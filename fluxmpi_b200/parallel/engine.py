@@ -106,10 +106,17 @@ class DataParallelEngine:
         self.offsets = offs
         buf_bytes = (cur * es + (1 << 21) - 1) >> 21 << 21
 
-        # ---- symmetric segment  [P | G]
+        # ---- symmetric segment  [P | G] (+ [2 parities][W] push slots for the one-shot flavour)
         self.p_off, self.g_off = 0, buf_bytes
+        # a model this small is latency-bound: every rank pushes its whole gradient to the peers,
+        # one barrier, everybody applies the whole rule (csrc/kernels/fused_step.cu, one-shot)
+        oneshot_max = int(float(os.environ.get("FMPI_FUSED_ONESHOT_KB", 2048)) * 1024)
+        self.oneshot = bool(self.native and self.world > 1 and F.hyper_for(self.rule) is not None
+                            and (algo == "oneshot" or (algo == "auto" and cur * es <= oneshot_max)))
+        self.stage_off = 2 * buf_bytes
+        self.stage_bytes = 2 * self.world * ((cur * es + 255) // 256 * 256) if self.oneshot else 0
         if self.native:
-            self.seg = self.dw.alloc_segment(2 * buf_bytes)
+            self.seg = self.dw.alloc_segment(2 * buf_bytes + self.stage_bytes)
             self.comm = self.dw.comm_for(self.seg, channel)
             rawP = self.dw.symm_tensor(self.seg, self.p_off, cur * es)
             rawG = self.dw.symm_tensor(self.seg, self.g_off, cur * es)
@@ -183,9 +190,13 @@ class DataParallelEngine:
         if blocks == 0 and self.world > 1 and self.native:
             self.blocks = int(os.environ.get("FMPI_FUSED_BLOCKS", 96))
         self.algo = _native.ALGO_NVLS if use_nvls else _native.ALGO_TWOSHOT
+        if self.oneshot:
+            self.algo = _native.ALGO_ONESHOT
+            bucket_mb = float("inf")            # one launch for the whole model
+            self.blocks = blocks
 
         # ---- buckets in backward (reverse registration) order
-        bucket_elems = max(int(bucket_mb * (1 << 20) / es), 1)
+        bucket_elems = cur if bucket_mb == float("inf") else max(int(bucket_mb * (1 << 20) / es), 1)
         if self.world == 1:
             bucket_elems = cur          # nothing to overlap with: one launch for the whole model
         self.buckets: list[_Bucket] = []
@@ -303,10 +314,17 @@ class DataParallelEngine:
             one = lambda t: C.byref(C.c_void_p(t.data_ptr())) if t is not None else None
             step_ptr = C.byref(C.c_void_p(self.step_dev.data_ptr()))
             code = F._dtype_code(self.dtype)
-            cuda_check(lib.fmpi_fused_step(
-                C.byref(self.comm), self.g_off, code, self.p_off, code, one(self.m), one(self.v),
-                one(self.master), b.lo, b.hi, C.byref(self.hyper), step_ptr,
-                C.byref(Launch(self.blocks, 0, self.algo)), stream.cuda_stream), "fused_step")
+            if self.oneshot:
+                cuda_check(lib.fmpi_fused_step_oneshot(
+                    C.byref(self.comm), self.g_off, self.p_off, code, one(self.m), one(self.v),
+                    one(self.master), b.lo, b.hi, C.byref(self.hyper), step_ptr, self.stage_off,
+                    self.stage_bytes, C.byref(Launch(self.blocks, 0, self.algo)), stream.cuda_stream),
+                    "fused_step_oneshot")
+            else:
+                cuda_check(lib.fmpi_fused_step(
+                    C.byref(self.comm), self.g_off, code, self.p_off, code, one(self.m), one(self.v),
+                    one(self.master), b.lo, b.hi, C.byref(self.hyper), step_ptr,
+                    C.byref(Launch(self.blocks, 0, self.algo)), stream.cuda_stream), "fused_step")
         else:
             code = F._dtype_code(self.dtype)
             es = self.G.element_size()
@@ -335,11 +353,18 @@ class DataParallelEngine:
             self._unfused_apply()
         self.steps_done += 1
         self._reset_buckets()
+        if self.native and self.world > 1:
+            self.dw.check_health()       # two host-memory reads: a lost peer surfaces here
+
+    def materialize_state(self):
+        """Build the lazily created per-leaf state of an unfused rule (no-op otherwise), so that
+        every rank walks a state tree of the same shape (checkpointing, synchronize)."""
+        if not self.fused and self.state_tree is None:
+            self.state_tree = [R.Leaf(self.rule, self.rule.init(p.data)) for p in self.params]
 
     def _unfused_apply(self):
         """Arbitrary rule: gradients were all-reduced in place by the kernel; apply with torch."""
-        if self.state_tree is None:
-            self.state_tree = [R.Leaf(self.rule, self.rule.init(p.data)) for p in self.params]
+        self.materialize_state()
         scale = 1.0 / self.world if self.average else 1.0
         with torch.no_grad():
             for leaf, p in zip(self.state_tree, self.params):
@@ -362,7 +387,7 @@ class DataParallelEngine:
     # ------------------------------------------------------------------ state access
     def owned_ranges(self) -> list[tuple[int, int]]:
         """Element ranges whose optimiser state this rank owns (one slice per bucket)."""
-        if not self.native:                 # replicated state: every rank holds all of it
+        if not self.native or self.oneshot:  # replicated state: every rank holds all of it
             return [(b.lo, b.hi) for b in self.buckets]
         es = self.P.element_size()
         n_per_vec = 16 // es
@@ -380,13 +405,14 @@ class DataParallelEngine:
         Owned slices are summed into zeros elsewhere — one all-reduce per moment."""
         out = {"step": int(self.step_dev.item()) if self.fused else self.steps_done}
         if not self.fused:
-            out["leaves"] = self.state_tree
+            self.materialize_state()
+            out["leaves"] = [leaf.state for leaf in self.state_tree]   # plain tensors / numbers / tuples
             return out
         for name in ("m", "v", "master"):
             t = getattr(self, name)
             if t is None:
                 continue
-            if not self.native:
+            if not self.native or self.oneshot:
                 out[name] = t.clone()
                 continue
             full = torch.zeros_like(t)
@@ -399,7 +425,9 @@ class DataParallelEngine:
 
     def load_state(self, state: dict):
         if not self.fused:
-            self.state_tree = state.get("leaves")
+            leaves = state.get("leaves")
+            self.state_tree = None if leaves is None else \
+                [R.Leaf(self.rule, st.state if isinstance(st, R.Leaf) else st) for st in leaves]
             self.steps_done = state.get("step", 0)
             return
         self.step_dev.fill_(int(state.get("step", 0)))

@@ -115,8 +115,7 @@ class HostDataParallelEngine:
                 1, ptr(self.P), ptr(self.G), ptr(self.m), ptr(self.v), n, code, self.code, self.hyper,
                 self.steps_done), "host_multi_tensor_step")
         else:
-            if self.state_tree is None:
-                self.state_tree = [R.Leaf(self.rule, self.rule.init(p.data)) for p in self.params]
+            self.materialize_state()
             scale = 1.0 / self.world if self.average else 1.0
             with torch.no_grad():
                 for leaf, p in zip(self.state_tree, self.params):
@@ -136,10 +135,17 @@ class HostDataParallelEngine:
             self.rule = R._adjust_rule(self.rule, eta, {})
 
     # ------------------------------------------------------------------ state access
+    def materialize_state(self):
+        """Per-leaf state of an unfused rule is created lazily; make it exist (same tree shape on
+        every rank before a checkpoint or a synchronize walks it)."""
+        if not self.fused and self.state_tree is None:
+            self.state_tree = [R.Leaf(self.rule, self.rule.init(p.data)) for p in self.params]
+
     def gather_state(self) -> dict:
         out = {"step": self.steps_done}
         if not self.fused:
-            out["leaves"] = self.state_tree
+            self.materialize_state()
+            out["leaves"] = [leaf.state for leaf in self.state_tree]
             return out
         for name in ("m", "v"):
             t = getattr(self, name)
@@ -150,7 +156,9 @@ class HostDataParallelEngine:
     def load_state(self, state: dict):
         self.steps_done = int(state.get("step", 0))
         if not self.fused:
-            self.state_tree = state.get("leaves")
+            leaves = state.get("leaves")
+            self.state_tree = None if leaves is None else \
+                [R.Leaf(self.rule, st.state if isinstance(st, R.Leaf) else st) for st in leaves]
             return
         for name in ("m", "v"):
             if name in state and getattr(self, name) is not None:

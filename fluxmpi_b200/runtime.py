@@ -307,10 +307,18 @@ def host_run(fn, *args):
     otherwise it takes its place behind the non-blocking calls already issued."""
     if not _S.initialized:
         raise FluxMPINotInitializedError()
-    if _S.host_pending > 0:
-        return host_submit(fn, *args).result()
-    with _S.host_exec:
-        return fn(*args)
+    try:
+        if _S.host_pending > 0:
+            return host_submit(fn, *args).result()
+        with _S.host_exec:
+            return fn(*args)
+    except _native.NativeError:
+        # the host world gave up on a peer (timeout / abort flag): kernels that are waiting for
+        # that peer's flags on this GPU must give up too, or they would spin until their own budget
+        dw = _S.device_world
+        if dw is not None:
+            dw.abort()
+        raise
 
 
 def _host_barrier_now():

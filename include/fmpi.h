@@ -213,13 +213,31 @@ typedef struct {
   uint32_t* sig[FMPI_MAX_RANKS];   /* symmetric signal pads (fmpi_sigpad_bytes() each) */
   void* mc_data;          /* multicast alias of the data window, or NULL */
   uint64_t data_bytes;    /* size of each data window */
+  uint32_t* ctrl;         /* device address of the health page from fmpi_health_page(), or NULL:
+                             word 0 = abort request (host -> kernels), word 1 = error (kernel ->
+                             host). NULL: waits are unbounded (single-GPU emulation) */
+  uint64_t timeout_ns;    /* budget of one cross-GPU wait; 0 = no time limit */
 } fmpi_devcomm;
+
+/* The health page: 64 bytes of pinned host memory mapped into the device (one per process and
+ * device, created on first use with that device current). A cross-GPU wait that has run out of
+ * fmpi_devcomm::timeout_ns sets word 1 and returns, and so does every other wait on this GPU
+ * from then on, so a lost peer ends in an error on the survivors instead of GPUs that spin
+ * inside a kernel for ever; the host can set word 0 to the same effect (it does when the host
+ * world reports a dead rank). After an error the data a collective produced is undefined.
+ *   fmpi_health_page   host and device address of the page
+ *   fmpi_health_check  0 = healthy; 1 = a wait was abandoned (fmpi_cuda_last_error says why) */
+int fmpi_health_page(uint32_t** host_ptr, uint32_t** dev_ptr);
+int fmpi_health_check(void);
+int fmpi_health_abort(void);
+int fmpi_health_reset(void);
 
 size_t fmpi_sigpad_bytes(void);
 
 /* Launch-shape hints; 0 = library default chosen from message size. */
 typedef struct { int32_t blocks; int32_t threads; int32_t algo; } fmpi_launch;
-enum { FMPI_ALGO_AUTO = 0, FMPI_ALGO_ONESHOT = 1, FMPI_ALGO_TWOSHOT = 2, FMPI_ALGO_NVLS = 3 };
+enum { FMPI_ALGO_AUTO = 0, FMPI_ALGO_ONESHOT = 1, FMPI_ALGO_TWOSHOT = 2, FMPI_ALGO_NVLS = 3,
+       FMPI_ALGO_PIPE = 4 /* chunk-pipelined staging (large ordinary buffers) */ };
 
 /* Collectives on buffers that already live in the symmetric window at byte offset `off`
  * (in-place, result in every rank's window for allreduce/bcast, root only for reduce). */
@@ -260,6 +278,17 @@ int fmpi_fused_step(const fmpi_devcomm* c, uint64_t g_off, int gdt, uint64_t p_o
                     float* const* m, float* const* v, float* const* master,
                     uint64_t lo, uint64_t hi, const fmpi_hyper* h, const int64_t* const* step_dev,
                     const fmpi_launch* l, fmpi_stream st);
+/* One-shot flavour for small buckets (a Quick-Start-sized model, README.md:37-38 of the
+ * reference): every rank pushes its gradient bucket into the peers' staging slots
+ * ([2 parities][world][slot] at stage_off, slot = stage_bytes / (2 * world) >= bucket bytes),
+ * one cross-GPU barrier, then every rank sums the W copies in rank order and applies the rule
+ * to the WHOLE bucket locally. The optimiser state is therefore replicated (m, v are updated
+ * everywhere), unlike fmpi_fused_step where only the owner of a slice touches them. */
+int fmpi_fused_step_oneshot(const fmpi_devcomm* c, uint64_t g_off, uint64_t p_off, int dtype,
+                            float* const* m, float* const* v, float* const* master, uint64_t lo,
+                            uint64_t hi, const fmpi_hyper* h, const int64_t* const* step_dev,
+                            uint64_t stage_off, uint64_t stage_bytes, const fmpi_launch* l,
+                            fmpi_stream st);
 int fmpi_step_advance(int64_t* step_dev, fmpi_stream st);
 
 /* Same rule math with no communication, over a table of scattered tensors (functional
@@ -285,7 +314,8 @@ int fmpi_checksum(const void* x, uint64_t nbytes, uint64_t* out, void* scratch, 
 /* fmpi_sumsq for callers that must not allocate device memory (no counterpart in the
  * reference, which has no device code of its own): a host runtime that owns the GPU memory
  * pool, a hook running inside a step whose memory is fully planned, a monitoring thread.
- * Same result as fmpi_sumsq, but the scratch is a 2304-byte array inside the library's device
+ * Same value as fmpi_sumsq up to fp64 summation order (it folds at most 256 partial sums where
+ * fmpi_sumsq folds up to 592), but the scratch is a 2304-byte array inside the library's device
  * image instead of a caller buffer, so the call performs no cudaMalloc / cudaFree / allocating
  * library call; the caller passes only the input and the 8-byte device output.
  *   - at most FMPI_NOALLOC_MAX_COUNT elements, more is refused with an error;
@@ -318,26 +348,6 @@ int fmpi_bn_backward(const void* dy, const void* y, const void* x, void* dx, voi
                      int C, int dtype, const float* gamma, const float* save_mean,
                      const float* save_invstd, float* dgamma, float* dbeta, int relu, void* scratch,
                      fmpi_stream st);
-
-/* forward without the statistics pass: the first 2*C floats of scratch already hold the
- * per-channel sum and sum of squares of x (left there by fmpi_conv1x1_bnstats). */
-int fmpi_bn_forward_presummed(const void* x, const void* res, void* y, uint64_t M, int C, int dtype,
-                              const float* gamma, const float* beta, float* running_mean,
-                              float* running_var, float momentum, float eps, int relu,
-                              float* save_mean, float* save_invstd, void* scratch, fmpi_stream st);
-
-/* ---- 1x1 convolution on channels-last activations as a tcgen05 GEMM with the BatchNorm
- * statistics in its epilogue (csrc/kernels/gemm_bnstats.cu; a separate library,
- * libfmpi_gemm.so, because it is built from the CUTLASS header tree):
- *   y[M, N] = x[M, K] * w[N, K]^T  (bf16, row-major; N and K multiples of 8)
- *   sum[N], sqs[N] (fp32) = column sums of the fp32 accumulators and of their squares.
- * EXPERIMENTAL: compiled and inspected, not yet run on a GPU; nothing uses it by default. */
-/* variant 0 (default): one SM per 128x64 tile; 1: CTA pairs on a 256x64 MMA tile (cta_group::2) */
-int fmpi_conv1x1_bnstats_variant(int variant);
-size_t fmpi_conv1x1_bnstats_workspace(int M, int N, int K);
-int fmpi_conv1x1_bnstats(const void* x, const void* w, void* y, float* sum, float* sqs, int M, int N,
-                         int K, void* workspace, size_t workspace_bytes, fmpi_stream st);
-const char* fmpi_gemm_last_error(void);
 
 /* ---- channels-last max pooling (csrc/kernels/pool.cu): x [N,H,W,C] -> y [N,OH,OW,C] with
  * OH = (H + 2P - K)/S + 1; idx keeps one byte per output element (window position of the

@@ -63,7 +63,8 @@ op_code(::typeof(max)) = Cint(3)
 op_code(f) = throw(FluxMPIError("unsupported reduction $f (use +, *, min, max)"))
 
 # typedef struct { int32 rank, world, emulate, channel; void* data[8]; uint32* sig[8];
-#                  void* mc_data; uint64 data_bytes; } fmpi_devcomm;
+#                  void* mc_data; uint64 data_bytes; uint32* ctrl; uint64 timeout_ns; } fmpi_devcomm;
+# (ctrl = device view of the health page: a lost peer ends a wait instead of hanging it)
 struct DevComm
     rank::Int32
     world::Int32
@@ -73,6 +74,8 @@ struct DevComm
     sig::NTuple{FMPI_MAX_RANKS, Ptr{Cvoid}}
     mc_data::Ptr{Cvoid}
     data_bytes::UInt64
+    ctrl::Ptr{Cvoid}
+    timeout_ns::UInt64
 end
 
 # typedef struct { int32 blocks, threads, algo; } fmpi_launch;

@@ -82,7 +82,11 @@ function _device_bringup(w::World, dev::Integer)
     data = pad([p + sig for p in peers])
     sigs = pad(peers)
     mcd = mcptr == C_NULL ? C_NULL : mcptr + sig
-    comms = [DevComm(w.rank, w.size, 0, ch, data, sigs, mcd, UInt64(size - sig)) for ch in 0:(FMPI_NUM_CHANNELS - 1)]
+    hp = Ref{Ptr{Cvoid}}(C_NULL)
+    dp = Ref{Ptr{Cvoid}}(C_NULL)
+    ccheck(ccall(csym(:fmpi_health_page), Cint, (Ptr{Ptr{Cvoid}}, Ptr{Ptr{Cvoid}}), hp, dp), "fmpi_health_page")
+    budget = UInt64(round(parse(Float64, get(ENV, "FMPI_DEVICE_TIMEOUT_S", get(ENV, "FMPI_TIMEOUT_S", "300"))) * 1e9))
+    comms = [DevComm(w.rank, w.size, 0, ch, data, sigs, mcd, UInt64(size - sig), dp[], budget) for ch in 0:(FMPI_NUM_CHANNELS - 1)]
     return DeviceWorld(h[], comms, 0, ar, ar, bc, mcptr != C_NULL)
 end
 

@@ -134,7 +134,7 @@ function FlatEngine(ps::CuVector{T}, rule; average::Bool=false, bucket_mb::Real=
     peers = [ccall(csym(:fmpi_symm_peer_ptr), Ptr{Cvoid}, (Ptr{Cvoid}, Cint), seg, q) for q in 0:(w.size - 1)]
     pad(v) = ntuple(i -> i <= length(v) ? v[i] : C_NULL, FMPI_MAX_RANKS)
     comm = DevComm(w.rank, w.size, 0, channel, pad(peers), base.sig, mcptr,
-                   UInt64(ccall(csym(:fmpi_symm_size), Csize_t, (Ptr{Cvoid},), seg)))
+                   UInt64(ccall(csym(:fmpi_symm_size), Csize_t, (Ptr{Cvoid},), seg)), base.ctrl, base.timeout_ns)
     loc = ccall(csym(:fmpi_symm_local_ptr), Ptr{Cvoid}, (Ptr{Cvoid},), seg)
     P = unsafe_wrap(CuArray, reinterpret(CuPtr{T}, UInt(loc)), n)
     G = unsafe_wrap(CuArray, reinterpret(CuPtr{T}, UInt(loc) + UInt(buf)), n)

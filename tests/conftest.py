@@ -42,3 +42,24 @@ def spmd():
             pytest.fail(f"{script} at W={nprocs} exited {code}\n{joined}")
         return outs
     return _run
+
+
+@pytest.fixture(autouse=True)
+def _device_waits_stay_healthy(request):
+    """After every GPU test: no cross-rank wait of a kernel may have been abandoned (a protocol
+    bug would otherwise pass as a slow test with wrong numbers, or hang without the bound)."""
+    yield
+    if request.node.get_closest_marker("gpu") is None:
+        return
+    import torch
+    if not torch.cuda.is_available():
+        return
+    from fluxmpi_b200 import _native
+    if _native.cuda_loaded():
+        torch.cuda.synchronize()
+        lib = _native.cuda()
+        rc = lib.fmpi_health_check()
+        if rc:
+            msg = lib.fmpi_cuda_last_error().decode()
+            lib.fmpi_health_reset()
+            pytest.fail("device health page: " + msg)

@@ -74,6 +74,44 @@ for _ in range(5):
 torch.cuda.synchronize()
 assert all(torch.equal(t, torch.full_like(t, float(w))) for t in ts)
 
+# a non-blocking all-reduce still in flight on the communication stream while a blocking one runs
+# on the current stream (legal MPI usage): the two channels have private staging
+big_a = torch.full((3 << 18,), float(r + 1), device=dev)
+big_b = torch.full((3 << 18,), float(2 * r + 1), device=dev)
+sm_a = torch.full((1000,), float(r + 1), device=dev)
+sm_b = torch.full((1000,), float(2 * r + 1), device=dev)
+for _ in range(4):
+    _, q1 = fm.Iallreduce(big_a, "sum")
+    fm.allreduce_(big_b, "sum")
+    _, q2 = fm.Iallreduce(sm_a, "max")
+    fm.allreduce_(sm_b, "max")
+    _, q3 = fm.Ibcast(sm_a, w - 1)
+    fm.bcast_(sm_b, 0)
+    fm.Waitall([q1, q2, q3])
+torch.cuda.synchronize()
+tri = w * (w + 1) / 2
+assert torch.equal(big_a, torch.full_like(big_a, tri * w ** 3)), big_a[:3]
+assert torch.equal(big_b, torch.full_like(big_b, (w * w) * w ** 3)), big_b[:3]
+assert torch.equal(sm_a, torch.full_like(sm_a, float(w))) and torch.equal(sm_b, torch.full_like(sm_b, 1.0))
+
+# push-mode kernels (one-shot all-reduce, staged broadcast) on the communication stream while the
+# SMs are busy with somebody else's work: blocks of one launch may start far apart in time and
+# must still agree on the call's parity
+if not quick:
+    busy = torch.randn(4096, 4096, device=dev)
+    xs = [torch.full((30000,), float(r + 1 + i), device=dev) for i in range(8)]
+    bs = [torch.full((300000,), float(r + i), device=dev) for i in range(8)]
+    reqs = []
+    for i in range(8):
+        for _ in range(6):
+            busy = (busy @ busy).clamp_(-1, 1)
+        reqs.append(fm.Iallreduce(xs[i], "sum")[1])
+        reqs.append(fm.Ibcast(bs[i], i % w)[1])
+    fm.Waitall(reqs, sync=True)
+    for i in range(8):
+        assert torch.equal(xs[i], torch.full_like(xs[i], tri + w * i)), (i, xs[i][:3])
+        assert torch.equal(bs[i], torch.full_like(bs[i], float(i % w + i))), (i, bs[i][:3])
+
 # non-contiguous / misaligned
 m = torch.arange(12, dtype=torch.float32, device=dev).reshape(3, 4).t()
 want = m.clone() * w

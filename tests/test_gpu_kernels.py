@@ -214,6 +214,82 @@ def test_symmetric_window_collectives(worlds, w):
             assert torch.equal(got[r], torch.full((n,), float(w - 1), device=DEV))
 
 
+# ------------------------------------------------------------------ chunk-pipelined kernels
+@pytest.mark.parametrize("w", [2, 3, 8])
+def test_pipelined_collectives_in_emulation(w):
+    """ALGO_PIPE (copy-in | link | copy-out roles handing chunks over through counters and
+    cross-rank flags; the peer-to-peer link flavour runs in emulation): all-reduce, reduce to a
+    root and broadcast over several chunks and slot reuses, back to back without host syncs,
+    with sizes that leave partial chunks and slices."""
+    ew = EmulatedWorld(w, DEV, window_mb=1, stage_mb=4)     # pipe region 1 MB => ~341 KB chunks
+    for rep, nbytes in enumerate((16 * w, 4096, 600_000 // 16 * 16, (3 << 20) + 16 * 7, 1 << 20)):
+        n = nbytes // 4
+        xs = make(torch.float32, n, w, seed=rep)
+        keep = [x.clone() for x in xs]
+        want = ref_reduce(torch.stack(xs), "sum")
+        outs = [torch.empty_like(x) for x in xs]
+        ew.allreduce(xs, _native.SUM, outs=outs, algo=_native.ALGO_PIPE)
+        root = rep % w
+        red = [x.clone() for x in xs]
+        ew.allreduce(red, _native.MAX, algo=_native.ALGO_PIPE, root=root)
+        bc = [torch.full((nbytes,), r + 1, dtype=torch.uint8, device=DEV) for r in range(w)]
+        ew.bcast(bc, root, algo=_native.ALGO_PIPE)
+        ew.allreduce(xs, _native.SUM, algo=_native.ALGO_PIPE)            # in place, right behind
+        torch.cuda.synchronize()
+        wmax = ref_reduce(torch.stack(keep), "max")
+        for r in range(w):
+            assert torch.allclose(outs[r].double(), want, rtol=1e-5, atol=1e-5), (w, nbytes, r)
+            assert torch.equal(outs[r], outs[0]) and torch.equal(xs[r], outs[r])
+            assert torch.equal(red[r].double(), wmax) if r == root else torch.equal(red[r], keep[r]), (w, nbytes, r)
+            assert torch.equal(bc[r], torch.full((nbytes,), root + 1, dtype=torch.uint8, device=DEV)), (w, nbytes, r)
+
+
+@pytest.mark.parametrize("w", [2, 3, 8])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float64, torch.int32])
+def test_pipelined_allreduce_dtypes_and_mixing_with_other_paths(w, dtype):
+    ew = EmulatedWorld(w, DEV, window_mb=1, stage_mb=4)
+    es = torch.empty((), dtype=dtype).element_size()
+    n = (1 << 20) // es + 16 * 3
+    small = make(torch.float32, 100, w, seed=5)
+    wsmall = ref_reduce(torch.stack(small), "sum")
+    for rep in range(3):
+        xs = make(dtype, n, w, seed=40 + rep)
+        want = ref_reduce(torch.stack(xs), "sum")
+        if not dtype.is_floating_point:
+            want = want.to(torch.int64).to(dtype).double()
+        ew.allreduce(xs, _native.SUM, algo=_native.ALGO_PIPE)
+        ys = [t.clone() for t in small]
+        ew.allreduce(ys, _native.SUM)                                    # one-shot in between
+        zs = make(torch.float32, 1 << 17, w, seed=60 + rep)
+        wz = ref_reduce(torch.stack(zs), "sum")
+        ew.allreduce(zs, _native.SUM, algo=_native.ALGO_TWOSHOT)         # staged two-shot in between
+        torch.cuda.synchronize()
+        tol = TOL.get(dtype, 0)
+        for r in range(w):
+            assert torch.allclose(xs[r].double(), want, rtol=tol, atol=tol) and torch.equal(xs[r], xs[0])
+            assert torch.allclose(ys[r].double(), wsmall, rtol=1e-5)
+            assert torch.allclose(zs[r].double(), wz, rtol=1e-5)
+
+
+@pytest.mark.parametrize("w", [2, 3, 8])
+def test_symmetric_bcast_pull_and_reemit(worlds, w):
+    """Mode 3 of the in-place broadcast: every rank loads its slice from the root's window and
+    stores it to all others (ALGO_PIPE selects it; AUTO does from 4 MB up)."""
+    ew = worlds(w)
+    for n in (4, 1000, (1 << 18) + 12):
+        off = ew.heap_alloc(n * 4 + 64)
+        got = [ew.window(r, off, n * 4).view(torch.float32) for r in range(w)]
+        for root in (0, w - 1):
+            src = torch.randn(n, device=DEV)
+            for r in range(w):
+                got[r].fill_(float(r))
+            got[root].copy_(src)
+            ew.bcast_symm(off, n * 4, root, algo=_native.ALGO_PIPE)
+            torch.cuda.synchronize()
+            for r in range(w):
+                assert torch.equal(got[r], src), (w, n, root, r)
+
+
 # ------------------------------------------------------------------ fused allreduce + optimiser
 def torch_reference(rule, p0, grads_per_step, dtype):
     """fp32 PyTorch restatement through the package's own rule objects (themselves checked
@@ -283,6 +359,56 @@ def test_fused_step_matches_reference(worlds, w, rule, dtype):
         assert torch.allclose(stitched, want, rtol=1e-4, atol=1e-5), (stitched - want).abs().max()
         assert torch.equal(P[0], stitched.to(dtype)), "bf16 parameters are the rounded master"
     assert int(step[0]) == 4
+
+
+@pytest.mark.parametrize("w", [2, 3, 8])
+@pytest.mark.parametrize("rule", RULES, ids=lambda r: type(r).__name__ if not isinstance(r, R.OptimiserChain) else "AdamW")
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_fused_step_oneshot_matches_reference(w, rule, dtype):
+    """One-shot flavour (push to all peers, one barrier, every rank applies the whole rule):
+    same numbers as the fp32 rule fed the summed gradient, replicated state on every rank,
+    parity slots reused over back-to-back steps."""
+    ew = EmulatedWorld(w, DEV, window_mb=8, stage_mb=1)
+    n = 64 * 257
+    es = 4 if dtype == torch.float32 else 2
+    p_off, g_off = ew.heap_alloc(n * es), ew.heap_alloc(n * es)
+    stage_bytes = 2 * w * (n * es)
+    stage_off = ew.heap_alloc(stage_bytes)
+    gen = torch.Generator().manual_seed(13)
+    p0 = torch.randn(n, generator=gen).to(dtype)
+    P = [ew.window(r, p_off, n * es).view(dtype) for r in range(w)]
+    G = [ew.window(r, g_off, n * es).view(dtype) for r in range(w)]
+    for r in range(w):
+        P[r].copy_(p0)
+    h = F.hyper_for(rule, zero_grad=True)
+    need_m, need_v = F.rule_needs(h)
+    m = [torch.zeros(n, device=DEV) for _ in range(w)] if need_m else None
+    v = [torch.zeros(n, device=DEV) for _ in range(w)] if need_v else None
+    master = [p0.float().to(DEV) for _ in range(w)] if dtype != torch.float32 else None
+    step = [torch.zeros(1, dtype=torch.int64, device=DEV) for _ in range(w)]
+    summed = []
+    for s in range(5):                                   # no host sync between steps 1..3
+        gs = [torch.randn(n, generator=gen).to(dtype) for _ in range(w)]
+        for r in range(w):
+            G[r].copy_(gs[r])
+        summed.append(torch.stack([g.float() for g in gs]).sum(0))
+        ew.fused_step_oneshot(g_off, p_off, dtype, m, v, master, 0, n, h, step, stage_off, stage_bytes,
+                              blocks=(0, 1, 3, 0, 2)[s])
+        for r in range(w):
+            _native.cuda_check(_native.cuda().fmpi_step_advance(step[r].data_ptr(), torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+    want = torch_reference(rule, p0, summed, dtype).to(DEV)
+    tol = 2e-5 if dtype == torch.float32 else 2e-2
+    for r in range(w):
+        assert int(G[r].float().abs().sum()) == 0, "gradient bucket must be cleared"
+        assert torch.allclose(P[r].float(), want, rtol=tol, atol=tol), (w, rule, (P[r].float() - want).abs().max())
+        assert torch.equal(P[r], P[0]), "replicas must be bit-identical"
+        if m is not None:
+            assert torch.equal(m[r], m[0]), "replicated first moment"
+        if v is not None:
+            assert torch.equal(v[r], v[0]), "replicated second moment"
+    if master is not None:
+        assert torch.allclose(master[0], want, rtol=1e-4, atol=1e-5)
 
 
 def test_fused_step_grad_scale_and_device_lr():

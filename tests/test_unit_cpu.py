@@ -300,13 +300,6 @@ def test_fused_ops_fall_back_to_stock_ops_off_gpu():
     img = torch.randn(2, 3, 32, 32)
     assert torch.allclose(a(img), b(img), atol=1e-5)
     assert sum(p.numel() for p in a.parameters()) == sum(p.numel() for p in b.parameters())
-    # the conv + BN-statistics fusion (ops/conv_bn.py) declines off GPU and changes nothing
-    c = resnet_tiny(fused_bn=True, fused_conv_bn=True)
-    c.load_state_dict(a.state_dict())
-    assert c.layer1[0].fused_conv_bn and list(c.state_dict()) == list(a.state_dict())
-    assert torch.allclose(c(img), a(img), atol=1e-6)
-    (c(img).sum()).backward()
-    assert c.layer1[0].conv1.weight.grad is not None
 
 
 def test_device_loader_cpu_shuffle_and_remainder():
@@ -390,156 +383,6 @@ def test_symmetric_lookup_and_dispatch_with_a_mock_library(monkeypatch):
     assert dw._symm_hit(FakeTensor(0x9000_0000 + (64 << 20) - 64, 1024)) is None
     assert dw._symm_hit(FakeTensor(0x10000 + 8, 1024)) is None
     assert dw.find_symmetric(FakeTensor(0x5000, 16)) is None
-
-
-@pytest.mark.parametrize("relu,res", [(True, False), (True, True), (False, True), (False, False)])
-def test_conv_bn_autograd_plumbing_with_stand_in_kernels(monkeypatch, relu, res):
-    """ops/conv_bn.py on CPU: its three native steps are replaced by plain-PyTorch versions of
-    what the kernels compute, so the autograd function around them — NHWC views, saved tensors,
-    dX = dY W, dW = dY^T X, the residual / ReLU gradient routing, running statistics — is
-    checked against F.conv2d + F.batch_norm without a GPU."""
-    from fluxmpi_b200.ops import conv_bn
-    from fluxmpi_b200.ops.batchnorm import FusedBatchNormAct
-
-    def nhwc(t):
-        return t.permute(0, 2, 3, 1).reshape(-1, t.shape[1])          # a view of channels_last memory
-
-    def gemm_stats(x, w2, y, scratch, M, N, K):
-        acc = nhwc(x).float() @ w2.float().t()
-        nhwc(y).copy_(acc.to(y.dtype))
-        scratch[:N] = acc.sum(0)
-        scratch[N:2 * N] = (acc * acc).sum(0)
-
-    def bn_fwd(y, residual, z, M, N, g, b, rm, rv, momentum, eps, relu_, mean, invstd, scratch):
-        m = scratch[:N].double() / M
-        var = (scratch[N:2 * N].double() / M - m * m).clamp_min(0)
-        mean.copy_(m)
-        invstd.copy_(1.0 / torch.sqrt(var + eps))
-        scale = (g if g is not None else 1.0) * invstd
-        shift = (b if b is not None else 0.0) - mean * scale
-        out = nhwc(y).float() * scale + shift
-        if residual is not None:
-            out = out + nhwc(residual).float()
-        nhwc(z).copy_((out.relu() if relu_ else out).to(z.dtype))
-        if rm is not None:
-            rm.mul_(1 - momentum).add_(momentum * mean)
-            rv.mul_(1 - momentum).add_(momentum * (var * M / (M - 1)).float())
-
-    def bn_bwd(dz, z, y, dy, dres, M, N, g, mean, invstd, dgamma, dbeta, relu_):
-        gz = nhwc(dz).float()
-        if relu_:
-            gz = gz * (nhwc(z).float() > 0)
-        if dres is not None:
-            nhwc(dres).copy_(gz.to(dres.dtype))
-        xhat = (nhwc(y).float() - mean) * invstd
-        dbeta.copy_(gz.sum(0))
-        dgamma.copy_((gz * xhat).sum(0))
-        scale = (g if g is not None else 1.0) * invstd
-        nhwc(dy).copy_((scale * (gz - dbeta / M - xhat * dgamma / M)).to(dy.dtype))
-
-    monkeypatch.setattr(conv_bn, "_k_gemm_stats", gemm_stats)
-    monkeypatch.setattr(conv_bn, "_k_bn_fwd", bn_fwd)
-    monkeypatch.setattr(conv_bn, "_k_bn_bwd", bn_bwd)
-    monkeypatch.setattr(conv_bn, "_scratch", lambda dev, N: torch.zeros(2 * N + 64))
-    monkeypatch.setattr(conv_bn, "eligible", lambda *a: True)
-
-    torch.manual_seed(3)
-    Bn, K, H, W, N = 3, 16, 5, 4, 24
-    conv = torch.nn.Conv2d(K, N, 1, bias=False).to(memory_format=torch.channels_last)
-    bn, ref_bn = FusedBatchNormAct(N, relu=relu), torch.nn.BatchNorm2d(N)
-    with torch.no_grad():
-        bn.weight.uniform_(0.5, 1.5)
-        bn.bias.uniform_(-0.5, 0.5)
-    ref_bn.load_state_dict(bn.state_dict())
-    x = torch.randn(Bn, K, H, W).contiguous(memory_format=torch.channels_last)
-    r = torch.randn(Bn, N, H, W).contiguous(memory_format=torch.channels_last) if res else None
-    xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
-    ra = r.clone().requires_grad_(True) if res else None
-    rb = r.clone().requires_grad_(True) if res else None
-    up = torch.randn(Bn, N, H, W)
-
-    z = conv_bn.conv1x1_bn_act(xa, conv, bn, ra)
-    got = torch.autograd.grad(z, [xa, conv.weight, bn.weight, bn.bias] + ([ra] if res else []), up)
-    t = ref_bn(torch.nn.functional.conv2d(xb, conv.weight))
-    t = t + rb if res else t
-    t = torch.relu(t) if relu else t
-    want = torch.autograd.grad(t, [xb, conv.weight, ref_bn.weight, ref_bn.bias] + ([rb] if res else []), up)
-
-    assert z.shape == t.shape and z.is_contiguous(memory_format=torch.channels_last)
-    assert torch.allclose(z, t, rtol=1e-4, atol=1e-5)
-    for a, b in zip(got, want):
-        assert a.shape == b.shape and torch.allclose(a, b, rtol=1e-3, atol=1e-4), float((a - b).abs().max())
-    assert torch.allclose(bn.running_mean, ref_bn.running_mean, atol=1e-6)
-    assert torch.allclose(bn.running_var, ref_bn.running_var, atol=1e-6)
-    assert int(bn.num_batches_tracked) == 1
-
-
-def test_register_buffer_bookkeeping_with_mock_cuda(monkeypatch):
-    """DeviceWorld.register_buffer / deregister_buffer with the CUDA driver, the IPC calls and
-    the host world replaced by recorders: handle exchange, per-peer pointers (base + that peer's
-    offset), the open-handle cache with reference counts, and the lookup that follows."""
-    import struct
-    import sys
-    import types
-    from fluxmpi_b200 import _native, runtime
-    from fluxmpi_b200.parallel import device_world as DW
-
-    opened, closed = [], []
-
-    class H:
-        reserved = b""
-
-    drv = types.SimpleNamespace(cuMemGetAddressRange=lambda p: (0, 0x7000_0000, 1 << 30))
-    rt = types.SimpleNamespace(
-        cudaIpcGetMemHandle=lambda base: (0, types.SimpleNamespace(reserved=b"L" * 64)),
-        cudaIpcMemHandle_t=H, cudaIpcMemLazyEnablePeerAccess=1,
-        cudaIpcOpenMemHandle=lambda h, flags: (opened.append(bytes(h.reserved)) or 0, 0x9000_0000),
-        cudaIpcCloseMemHandle=lambda p: (closed.append(p) or 0,))
-    pkg = types.ModuleType("cuda.bindings")
-    pkg.driver, pkg.runtime = drv, rt
-    monkeypatch.setitem(sys.modules, "cuda.bindings", pkg)
-    monkeypatch.setitem(sys.modules, "cuda.bindings.driver", drv)
-    monkeypatch.setitem(sys.modules, "cuda.bindings.runtime", rt)
-
-    class FakeTensor:
-        is_cuda, requires_grad, dtype = True, False, torch.float32
-
-        def __init__(self, ptr, n): self.ptr, self.n = ptr, n
-        def data_ptr(self): return self.ptr
-        def numel(self): return self.n
-        def element_size(self): return 4
-        def is_contiguous(self): return True
-
-    dw = DW.DeviceWorld(0, 2, 0, "job")
-    dw.native = True
-    dw.base = DW.Segment(None, 0x1000, 1 << 20, [0x1000, 0x2000], 0, "vmm")
-    peer = b"P" * 64 + struct.pack("<QQQ", 4096, 1 << 20, 1)          # rank 1: offset 4096 in its block
-    monkeypatch.setattr(runtime, "host_allgather_bytes",
-                        lambda blob, size=None: [blob, peer] if len(blob) == 88 else [blob, blob])
-    monkeypatch.setattr(runtime, "host_barrier", lambda: None)
-    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a, **k: None)
-
-    t = FakeTensor(0x7000_0000 + 256, (1 << 20) // 4)
-    reg = dw.register_buffer(t)
-    assert reg is not None and opened == [b"P" * 64]
-    comm = reg[3][0]
-    assert comm.world == 2 and comm.rank == 0 and comm.data[0] == t.data_ptr()
-    assert comm.data[1] == 0x9000_0000 + 4096 and comm.sig[1] == 0x2000 and not comm.mc_data
-    hit = dw._symm_hit(FakeTensor(t.data_ptr() + 1024, 256))
-    assert hit is not None and hit[1] == 1024 and hit[2] is False
-    reg2 = dw.register_buffer(FakeTensor(0x7000_0000 + 256, (1 << 20) // 4))   # same peer block: cached
-    assert reg2 is not None and len(opened) == 1
-    dw.deregister_buffer(reg)
-    assert closed == [] and dw._symm_hit(t) is not None                         # still held by reg2
-    dw.deregister_buffer(reg2)
-    assert closed == [0x9000_0000] and dw._symm_hit(t) is None
-    # sizes that differ between ranks, or an unaligned tensor, are refused on every rank
-    monkeypatch.setattr(runtime, "host_allgather_bytes",
-                        lambda blob, size=None: [blob, b"P" * 64 + struct.pack("<QQQ", 0, 512, 1)]
-                        if len(blob) == 88 else [blob, blob])
-    with pytest.warns(UserWarning):
-        assert dw.register_buffer(t) is None
-    assert len(opened) == 1
 
 
 def test_launcher_helpers():
