@@ -22,7 +22,13 @@ from .. import _native
 from .._native import Launch
 
 _ALGO = {"auto": _native.ALGO_AUTO, "oneshot": _native.ALGO_ONESHOT, "twoshot": _native.ALGO_TWOSHOT,
-         "nvls": _native.ALGO_NVLS}
+         "nvls": _native.ALGO_NVLS, "pipe": _native.ALGO_PIPE}
+
+# Sizes from which the library's own choice (FMPI_ALGO_AUTO) is a kernel family the round-1 grids
+# never measured: the chunk-pipelined staged kernels for ordinary buffers and the pull + re-emit
+# broadcast on symmetric memory (csrc/kernels/collectives.cu: pipe_cfg(), bcast_mode()). A table
+# without "pipe" rows must not shadow them; a re-measured table (rows with "algo": "pipe") may.
+_AUTO_FROM = {"allreduce_any": 48 << 20, "reduce_any": 8 << 20, "bcast_any": 8 << 20, "bcast_symm": 4 << 20}
 
 
 class Tuner:
@@ -42,12 +48,16 @@ class Tuner:
                       if r["algo"] != "nvls" or multicast]
                 if ok:
                     self.table[op] = sorted(ok)
+        self.auto_from = {op: lim for op, lim in _AUTO_FROM.items()
+                          if not any(r[1] == "pipe" for r in self.table.get(op, ()))}
 
     def choice(self, op: str, nbytes: int):
         """(algo name, blocks, threads) or None."""
         rows = self.table.get(op)
         if not rows or nbytes <= 0 or nbytes * 2 < rows[0][0]:
             return None          # below the measured range: the library's latency defaults apply
+        if nbytes >= self.auto_from.get(op, 1 << 62):
+            return None          # the library's large-message kernels (see _AUTO_FROM)
         lg = math.log2(nbytes)
         best = min(rows, key=lambda r: abs(math.log2(r[0]) - lg))
         return best[1], best[2], best[3]
