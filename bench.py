@@ -17,6 +17,12 @@ Arms (--impl):
   refshape   the reference's step shape on this box's software (SURVEY §6 "reference-shaped"):
              per leaf D2H, blocking host all-reduce, H2D, then the rule as per-leaf array ops.
 
+The `ours` arm also times, in the same invocation on the same GPUs, three forms of the DDP
+baseline (`ddp_same_run`: stock modules eager; stock modules with the whole step in a CUDA graph;
+DDP over this repo's fused BatchNorm modules) and divides by the strongest for `vs_baseline`;
+at N >= 2 it first runs the device self-test through the live world (`selftest`) and a short
+all-reduce bandwidth probe against NCCL (`collectives`).
+
 One JSON line on rank 0. `value` = whole-job images/s over the device-timed steps (CUDA events,
 max over ranks); `e2e` = the same through the public API with a pinned-host→device copy of every
 step's inputs and a device→host read of every step's loss inside the timed region.
@@ -50,6 +56,8 @@ def parse():
     ap.add_argument("--no-overlap", action="store_true")
     ap.add_argument("--no-fused-bn", action="store_true",
                     help="ours: use stock nn.BatchNorm2d + ReLU instead of the fused channels-last kernels")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="ours: skip the same-run DDP baselines, the self-test and the collectives probe")
     ap.add_argument("--bucket-mb", type=float, default=32.0)
     ap.add_argument("--algo", default="auto")
     return ap.parse_args()
@@ -153,16 +161,6 @@ def preprocess(xb, dtype):
     return x.to(dtype).sub_(127.5).mul_(1.0 / 58.0)
 
 
-def baseline_number(model: str, n: int):
-    p = ROOT / "baseline" / "ddp_measured.json"
-    if not p.exists():
-        return None
-    try:
-        return json.loads(p.read_text()).get(model, {}).get(str(n))
-    except (ValueError, OSError):
-        return None
-
-
 def dist_max(value: float, impl: str) -> float:
     """max over ranks of a python float"""
     import torch
@@ -193,6 +191,102 @@ def timed(run_steps, k: int, barrier, impl: str):
     return dist_max(e0.elapsed_time(e1), impl)
 
 
+# ------------------------------------------------------------------------------ same-run baselines
+def _nccl_group(rank, world, dev):
+    import torch.distributed as dist
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    return dist
+
+
+def ddp_arm(a, rank, world, dev, dx, dy, steps, fused_bn=False, graph=False):
+    """torch DDP + NCCL + torch.optim.Adam(fused=True) on the same model / dtype / layout /
+    inputs, timed like our arm (CUDA events, max over ranks). ``graph``: the whole step
+    (forward, backward with the bucketed NCCL all-reduces, optimiser) replayed as one CUDA graph —
+    the strongest form of the baseline. Returns {"img_s", "ms_per_step"} or {"error"}."""
+    import gc
+    import torch
+    from torch.nn.parallel import DistributedDataParallel as DDP
+    dist = _nccl_group(rank, world, dev)
+    cdt = torch.bfloat16 if a.dtype == "bf16" else torch.float32
+    barrier = (lambda: dist.barrier()) if world > 1 else (lambda: None)
+
+    def measure():
+        torch.manual_seed(0)
+        model = make_model(a.model, fused_bn=fused_bn).to(dev).to(memory_format=torch.channels_last)
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            net = DDP(model, device_ids=[dev.index], gradient_as_bucket_view=True) if world > 1 else model
+            opt = torch.optim.Adam(model.parameters(), lr=1e-3, fused=True, capturable=graph)
+
+            def step():
+                x = preprocess(dx, torch.float32)
+                with torch.autocast("cuda", dtype=cdt, enabled=a.dtype == "bf16"):
+                    loss = torch.nn.functional.cross_entropy(net(x), dy)
+                loss.backward()
+                opt.step()
+                return loss
+
+            for _ in range(11 if (graph and world > 1) else max(a.warmup, 3)):
+                opt.zero_grad(set_to_none=True)
+                step()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        if graph:
+            g = torch.cuda.CUDAGraph()
+            opt.zero_grad(set_to_none=True)
+            with torch.cuda.graph(g):
+                step()
+            run_one = g.replay
+        else:
+            def run_one():
+                opt.zero_grad(set_to_none=True)
+                step()
+        for _ in range(2):
+            run_one()
+        ms = timed(lambda k: [run_one() for _ in range(k)], steps, barrier, "ddp")
+        return {"img_s": round(a.batch * world * steps / (ms / 1e3), 1), "ms_per_step": round(ms / steps, 3)}
+
+    try:
+        out = measure()
+    except Exception as e:                                        # noqa: BLE001
+        out = {"error": f"{type(e).__name__}: {str(e)[:160]}"}
+    gc.collect()
+    torch.cuda.empty_cache()
+    return out
+
+
+def collectives_probe(rank, world, dev):
+    """All-reduce bus bandwidth (GB/s, 2(W-1)/W * bytes / time; CUDA events, max over ranks) at
+    three sizes: ours on an ordinary tensor, ours on symmetric memory, NCCL on an ordinary tensor."""
+    import torch
+    import fluxmpi_b200 as fm
+    dist = _nccl_group(rank, world, dev)
+    out = {}
+    for nbytes in (1 << 20, 64 << 20, 256 << 20):
+        n = nbytes // 4
+        iters = 20 if nbytes <= (1 << 20) else 8
+        x = torch.ones(n, device=dev)
+        sx = fm.symm_empty((n,), torch.float32)
+        sx.fill_(1.0)
+        row = {}
+        for name, fn, buf in (("ours", lambda t: fm.allreduce_(t, "sum"), x),
+                              ("ours_symmetric", lambda t: fm.allreduce_(t, "sum"), sx),
+                              ("nccl", lambda t: dist.all_reduce(t), x)):
+            for _ in range(3):
+                fn(buf)
+            ms = timed(lambda k: [fn(buf) for _ in range(k)], iters, fm.barrier, "ours") / iters
+            row[name] = round(nbytes / (ms * 1e-3) * 2 * (world - 1) / world / 1e9, 1)
+            buf.fill_(1.0)
+        out[f"{nbytes >> 20}MB"] = row
+        del x
+        torch.cuda.empty_cache()
+    return out
+
+
 # ------------------------------------------------------------------------------ our arm
 def run_ours(a):
     import torch
@@ -207,6 +301,11 @@ def run_ours(a):
     assert world == a.gpus, f"--gpus {a.gpus} but WORLD_SIZE={world}"
     dev = fm.current_device()
     cdt = torch.bfloat16 if a.dtype == "bf16" else torch.float32
+
+    selftest = collectives = None
+    if world > 1 and not a.no_extras:
+        selftest = fm.selftest.run()                 # every kernel family through the live world
+        collectives = collectives_probe(rank, world, dev)
 
     torch.manual_seed(rank)
     model = make_model(a.model, fused_bn=not a.no_fused_bn).to(dev).to(memory_format=torch.channels_last)
@@ -298,8 +397,25 @@ def run_ours(a):
     gb = a.batch * world
     value = gb * a.steps / (ms / 1e3)
     e2e = gb * a.steps / (ms_e2e / 1e3)
-    base = baseline_number(a.model, world)
     dw = fm.runtime.state().device_world
+    comm_desc = f"{dw.mode}{'+nvls' if engine.algo == _native.ALGO_NVLS else ''}"
+    n_buckets, launches_per_step = len(engine.buckets), int(launches) // max(a.steps, 1)
+    # ---- the baseline, measured now, here: release our arm's memory first
+    ddp_same_run, base = None, None
+    if not a.no_extras:
+        engine.close()
+        do_step = step_fn = engine = model = loader = data = None     # noqa: F841 (drop the references)
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+        k = max(5, min(a.steps, 20))
+        ddp_same_run = {"eager": ddp_arm(a, rank, world, dev, dx, dy, k),
+                        "fused_bn": ddp_arm(a, rank, world, dev, dx, dy, k, fused_bn=True),
+                        "graph": ddp_arm(a, rank, world, dev, dx, dy, k, graph=True)
+                        if (world == 1 or os.environ.get("FMPI_BENCH_DDP_GRAPH", "1") != "0")
+                        else {"error": "skipped (FMPI_BENCH_DDP_GRAPH=0)"}}
+        got = [v["img_s"] for v in ddp_same_run.values() if "img_s" in v]
+        base = max(got) if got else None
     if rank == 0:
         print(json.dumps({
             "metric": "ResNet-50 train images/s (synthetic 224x224, data-parallel)", "impl": "ours",
@@ -310,14 +426,20 @@ def run_ours(a):
                        "seq_len": None, "parallelism": f"dp{world}", "optimizer": "Adam(1e-3), fused with the gradient all-reduce",
                        "layout": "channels_last", "cuda_graph": not a.no_graph, "overlap": not a.no_overlap,
                        "batchnorm": "stock nn.BatchNorm2d" if a.no_fused_bn else "fused channels-last BN(+add)(+ReLU) kernels (ours)",
-                       "bucket_mb": a.bucket_mb, "buckets": len(engine.buckets),
-                       "comm": f"{dw.mode}{'+nvls' if engine.algo == _native.ALGO_NVLS else ''}",
+                       "bucket_mb": a.bucket_mb, "buckets": n_buckets, "comm": comm_desc,
                        "l2": "per-step working set (activations of 256 images + 205 MB of parameters and gradients) far exceeds the 126 MB L2; no explicit flush",
-                       "baseline": "vs_baseline divides by baseline/ddp_measured.json (torch DDP+NCCL, our measurement); the reference publishes no number"},
+                       "baseline": "vs_baseline = value / the strongest of ddp_same_run (torch DDP + NCCL + fused Adam timed in this run on these GPUs: eager, CUDA graph, with our fused BN modules); the reference publishes no number"},
             "e2e": {"value": round(e2e, 1), "unit": "img/s", "ms_per_step": round(ms_e2e / a.steps, 3),
                     "h2d_bytes_per_step": int(h2d_per_step), "d2h_bytes_per_step": 4},
-            "gpu_launches": int(launches), "final_loss": final_loss, "clocks": clocks}))
-    engine.close()
+            "gpu_launches": int(launches), "gpu_launches_per_step": launches_per_step,
+            "final_loss": final_loss * world, "final_loss_note": "unscaled mean cross-entropy of rank 0's last batch (the step itself scales the loss by 1/W: SUM semantics)",
+            "ddp_same_run": ddp_same_run, "selftest": selftest, "collectives": collectives,
+            "clocks": clocks}))
+    if engine is not None:
+        engine.close()
+    import torch.distributed as dist
+    if dist.is_initialized():
+        dist.destroy_process_group()
     fm.Finalize()
 
 

@@ -31,6 +31,7 @@ from .runtime import (Init, Initialized, Finalize, local_rank, total_workers, no
 from .comm import (allreduce_, bcast_, reduce_, Iallreduce, Ibcast, Request, Waitall, barrier,
                    cpu, gpu, COMM_WORLD, symm_empty, symm_zeros, is_symmetric,
                    shm_empty, shm_free)
+from .group import Group
 from .tree import fmap, functor
 from . import rules
 from .rules import (AbstractRule, Leaf, setup, update, update_, adjust, Descent, Momentum,
@@ -51,6 +52,9 @@ def __getattr__(name):
     if name == "DataParallelEngine":
         from .parallel.engine import DataParallelEngine
         return DataParallelEngine
+    if name == "selftest":
+        import importlib
+        return importlib.import_module(".selftest", __name__)
     if name in ("HostDataParallelEngine", "make_engine"):
         from .parallel import host_engine
         return getattr(host_engine, name)

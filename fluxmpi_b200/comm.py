@@ -13,8 +13,9 @@ Reference (citations into /root/reference/src/mpi_extensions.jl):
 Differences by design: device tensors are never staged through the host — they go
 to the NVLink peer-to-peer kernels of ``libfmpi_cuda.so`` (or NCCL when P2P support has been
 disabled with :func:`fluxmpi_b200.disable_p2p_support`); all calls are truly in place *and*
-return the tensor, so both calling styles of the reference work. ``comm`` is accepted and
-ignored (there is one world, like the reference's hard-coded ``MPI.COMM_WORLD``).
+return the tensor, so both calling styles of the reference work. ``comm`` is ``COMM_WORLD`` or a
+:class:`fluxmpi_b200.Group` (a rank subset with its own host world and device signal pads);
+roots are ranks within ``comm``, as in MPI.
 """
 from __future__ import annotations
 
@@ -26,6 +27,7 @@ import numpy as np
 import torch
 
 from . import _native, runtime
+from . import group as _group
 from ._native import op_code
 from .utils import trace as _trace
 
@@ -180,13 +182,25 @@ def _host_symm_hit(t: torch.Tensor):
     return None
 
 
-def _host_allreduce_now(send: torch.Tensor, recv: torch.Tensor, op: int):
-    S = runtime.state()
+class _HC:
+    """host communicator view: (handle, rank, world) of the world or of a Group"""
+    __slots__ = ("host_comm", "rank", "world", "is_world")
+
+    def __init__(self, grp=None):
+        S = runtime.state()
+        if grp is None:
+            self.host_comm, self.rank, self.world, self.is_world = S.host_comm, S.rank, S.world, True
+        else:
+            self.host_comm, self.rank, self.world, self.is_world = grp.host_comm, grp.rank, grp.size, False
+
+
+def _host_allreduce_now(send: torch.Tensor, recv: torch.Tensor, op: int, grp=None):
+    S = _HC(grp)
     if S.world == 1:
         if recv.data_ptr() != send.data_ptr():
             recv.copy_(send)
         return
-    if send.data_ptr() == recv.data_ptr() and send.dtype != torch.bool:
+    if S.is_world and send.data_ptr() == recv.data_ptr() and send.dtype != torch.bool:
         hit = _host_symm_hit(recv)
         if hit is not None:
             _native.host_check(
@@ -216,11 +230,11 @@ def _host_allreduce_many_now(ts, op: int):
                                                 dtype_code(ts[0].dtype), op), "allreduce_many")
 
 
-def _host_bcast_now(buf: torch.Tensor, root: int):
-    S = runtime.state()
+def _host_bcast_now(buf: torch.Tensor, root: int, grp=None):
+    S = _HC(grp)
     if S.world == 1:
         return
-    hit = _host_symm_hit(buf)
+    hit = _host_symm_hit(buf) if S.is_world else None
     if hit is not None:            # symmetric host memory: copied straight out of the root's block
         _native.host_check(
             _native.host().fmpi_host_bcast_symm(S.host_comm, hit[0], hit[1], buf.numel() * buf.element_size(),
@@ -234,8 +248,8 @@ def _host_bcast_now(buf: torch.Tensor, root: int):
         buf.copy_(b)
 
 
-def _host_reduce_now(send: torch.Tensor, recv: torch.Tensor, op: int, root: int):
-    S = runtime.state()
+def _host_reduce_now(send: torch.Tensor, recv: torch.Tensor, op: int, root: int, grp=None):
+    S = _HC(grp)
     if S.world == 1:
         if recv.data_ptr() != send.data_ptr():
             recv.copy_(send)
@@ -277,12 +291,13 @@ def _resolve_op(op):
         raise
 
 
-def _host_custom_now(send: torch.Tensor, recv: torch.Tensor, fn, root: int):
+def _host_custom_now(send: torch.Tensor, recv: torch.Tensor, fn, root: int, grp=None):
     """Reduction with a user function: all-gather the operands, fold them in rank order on
     every rank (same order everywhere, hence the same bits). ``root < 0`` = all ranks keep the
     result. W copies of the message live on each rank while this runs: meant for the odd custom
     reduction, not for gradients."""
-    S = runtime.state()
+    S = _HC(grp)
+    slot_bytes = runtime.state().slot_bytes
     s, _ = _host_view(send)
     if S.world == 1:
         if recv.data_ptr() != s.data_ptr():
@@ -291,7 +306,7 @@ def _host_custom_now(send: torch.Tensor, recv: torch.Tensor, fn, root: int):
     raw = s.reshape(-1).view(torch.uint8) if s.dtype != torch.bool else s.reshape(-1).to(torch.uint8)
     n, W = raw.numel(), S.world
     parts = torch.empty(W, n, dtype=torch.uint8)
-    chunk = max(1, S.slot_bytes // W)
+    chunk = max(1, slot_bytes // W)
     tmp = torch.empty(W * chunk, dtype=torch.uint8)
     lib = _native.host()
     for off in range(0, n, chunk):
@@ -309,16 +324,16 @@ def _host_custom_now(send: torch.Tensor, recv: torch.Tensor, fn, root: int):
         recv.copy_(torch.as_tensor(acc).reshape(recv.shape))
 
 
-def _custom(send: torch.Tensor, recv: torch.Tensor, fn, root: int = -1):
+def _custom(send: torch.Tensor, recv: torch.Tensor, fn, root: int = -1, grp=None):
     if recv.is_cuda:                       # staged through the host, as the reference's MPI would
         h = send.detach().cpu()
         out = h.clone()
-        runtime.host_run(_host_custom_now, h, out, fn, root)
-        if root < 0 or runtime.local_rank() == root:
+        runtime.host_run(_host_custom_now, h, out, fn, root, grp)
+        if root < 0 or _HC(grp).rank == root:
             with torch.no_grad():
                 recv.copy_(out)
     else:
-        runtime.host_run(_host_custom_now, send.detach(), recv.detach(), fn, root)
+        runtime.host_run(_host_custom_now, send.detach(), recv.detach(), fn, root, grp)
 
 
 def _count(kind: str, t: torch.Tensor) -> None:
@@ -326,68 +341,82 @@ def _count(kind: str, t: torch.Tensor) -> None:
 
 
 def allreduce_(v, op="sum", comm=COMM_WORLD):
-    """In-place all-reduce of ``v`` with ``op``; returns ``v``.
+    """In-place all-reduce of ``v`` with ``op`` over ``comm``; returns ``v``.
 
     CPU tensors / numpy arrays: POSIX-shm backend. CUDA tensors: NVLink P2P kernel enqueued on
     the current stream (stream-ordered, like every torch op). ``op`` may also be any callable
     ``f(a, b)`` on tensors (gathered and folded in rank order)."""
     if not runtime.Initialized():
         raise runtime.FluxMPINotInitializedError()
+    grp = _group.resolve(comm)
     t = _as_tensor(v)
     code, fn = _resolve_op(op)
     _count("allreduce", t)
     if fn is not None:
-        _custom(t, t, fn)
+        _custom(t, t, fn, grp=grp)
         return v
     dtype_code(t.dtype)
     if t.is_cuda:
-        _device_world().allreduce(t, code)
+        _device_world().allreduce(t, code, group=grp)
     else:
-        runtime.host_run(_host_allreduce_now, t, t, code)
+        runtime.host_run(_host_allreduce_now, t, t, code, grp)
     return v
 
 
 def bcast_(v, root: int = 0, comm=COMM_WORLD):
-    """In-place broadcast of ``v`` from ``root``; returns ``v``."""
+    """In-place broadcast of ``v`` from ``root`` (a rank within ``comm``); returns ``v``."""
     if not runtime.Initialized():
         raise runtime.FluxMPINotInitializedError()
+    grp = _group.resolve(comm)
     t = _as_tensor(v)
-    _check_root(root)
+    _check_root(root, grp)
     _count("bcast", t)
     if t.is_cuda:
-        _device_world().bcast(t, root)
+        _device_world().bcast(t, root, group=grp)
     else:
-        runtime.host_run(_host_bcast_now, t, root)
+        runtime.host_run(_host_bcast_now, t, root, grp)
     return v
 
 
 def reduce_(v, op="sum", root: int = 0, comm=COMM_WORLD):
-    """Reduce to ``root`` in place; non-root buffers are left untouched. Returns ``v``."""
+    """Reduce to ``root`` (a rank within ``comm``) in place; non-root buffers are left untouched.
+    Returns ``v``."""
     if not runtime.Initialized():
         raise runtime.FluxMPINotInitializedError()
+    grp = _group.resolve(comm)
     t = _as_tensor(v)
     code, fn = _resolve_op(op)
-    _check_root(root)
+    _check_root(root, grp)
     _count("reduce", t)
     if fn is not None:
-        _custom(t, t, fn, root)
+        _custom(t, t, fn, root, grp)
         return v
     dtype_code(t.dtype)
     if t.is_cuda:
-        _device_world().reduce(t, code, root)
+        _device_world().reduce(t, code, root, group=grp)
     else:
-        runtime.host_run(_host_reduce_now, t, t, code, root)
+        runtime.host_run(_host_reduce_now, t, t, code, root, grp)
     return v
 
 
+def _group_barrier_now(grp):
+    if grp.size > 1:
+        _native.host_check(_native.host().fmpi_host_barrier(grp.host_comm), "group barrier")
+
+
 def barrier(comm=COMM_WORLD):
-    """Host barrier (``MPI.Barrier``)."""
-    runtime.host_barrier()
+    """Host barrier (``MPI.Barrier``) over ``comm``."""
+    grp = _group.resolve(comm)
+    if grp is None:
+        runtime.host_barrier()
+    else:
+        runtime.host_run(_group_barrier_now, grp)
 
 
-def _check_root(root: int):
-    if not (0 <= int(root) < runtime.total_workers()):
-        raise ValueError(f"root {root} out of range for {runtime.total_workers()} workers")
+def _check_root(root: int, grp=None):
+    n = runtime.total_workers() if grp is None else grp.size
+    if not (0 <= int(root) < n):
+        raise ValueError(f"root {root} out of range for {n} workers")
 
 
 # ------------------------------------------------------------------------------ non-blocking API
@@ -404,21 +433,22 @@ def Iallreduce(*args, comm=COMM_WORLD):
         (recv, op), send = args, args[0]
     else:
         raise TypeError("Iallreduce(send, recv, op) or Iallreduce(buf, op)")
+    grp = _group.resolve(comm)
     s, r = _as_tensor(send), _as_tensor(recv)
     _check_pair(s, r)
     code, fn = _resolve_op(op)
     _count("iallreduce", r)
     if fn is not None:                      # custom function: host path, queued like the others
         if r.is_cuda:
-            _custom(s, r, fn)
+            _custom(s, r, fn, grp=grp)
             return recv, Request(buffer=recv)
-        fut = runtime.host_submit(_host_custom_now, s.detach(), r.detach(), fn, -1)
+        fut = runtime.host_submit(_host_custom_now, s.detach(), r.detach(), fn, -1, grp)
         return recv, Request(future=fut, buffer=recv)
     dtype_code(s.dtype)
     if r.is_cuda:
-        ev = _device_world().allreduce_async(s, r, code)
+        ev = _device_world().allreduce_async(s, r, code, group=grp)
         return recv, Request(event=ev, buffer=recv)
-    fut = runtime.host_submit(_host_allreduce_now, s, r, code)
+    fut = runtime.host_submit(_host_allreduce_now, s, r, code, grp)
     return recv, Request(future=fut, buffer=recv)
 
 
@@ -426,13 +456,14 @@ def Ibcast(buf, root: int = 0, comm=COMM_WORLD):
     """Non-blocking broadcast → ``(buf, request)``."""
     if not runtime.Initialized():
         raise runtime.FluxMPINotInitializedError()
+    grp = _group.resolve(comm)
     b = _as_tensor(buf)
-    _check_root(root)
+    _check_root(root, grp)
     _count("ibcast", b)
     if b.is_cuda:
-        ev = _device_world().bcast_async(b, root)
+        ev = _device_world().bcast_async(b, root, group=grp)
         return buf, Request(event=ev, buffer=buf)
-    fut = runtime.host_submit(_host_bcast_now, b, root)
+    fut = runtime.host_submit(_host_bcast_now, b, root, grp)
     return buf, Request(future=fut, buffer=buf)
 
 

@@ -517,7 +517,61 @@ class DeviceWorld(_Base):
             return None
         return hit
 
-    def allreduce(self, t: torch.Tensor, op: int, launch=None):
+    # ------------------------------------------------------------------ rank groups
+    def _group_call(self, kind: str, t: torch.Tensor, op: int, root: int, group, channel: int = 0, stream=None):
+        """A collective over a rank subset (fm.Group). Native worlds: the staged kernels on the
+        group's own communicator (its signal pads, the members' windows only), bracketed by two
+        device barriers among the members so that it can follow or precede collectives of any
+        other communicator on this GPU's staging window. Otherwise: through the group's host world."""
+        if group.size == 1 or t.numel() == 0:
+            return t
+        if not self.native:
+            h = t.detach().cpu()
+            from .. import comm as _comm
+            {"allreduce": lambda: _comm._host_allreduce_now(h, h, op, group),
+             "reduce": lambda: _comm._host_reduce_now(h, h, op, root, group),
+             "bcast": lambda: _comm._host_bcast_now(h, root, group)}[kind]()
+            if kind == "allreduce" or (kind == "reduce") == (group.rank == root):
+                self._copy_back(t, h.to(t.device))
+            return t
+        self.check_health()
+        lib = self._lib
+        ref = group.device_refs()[channel]
+        st = (torch.cuda.current_stream() if stream is None else stream).cuda_stream
+        w, copy = self._work_tensor(t)
+        nbytes = w.numel() * w.element_size()
+        cuda_check(lib.fmpi_barrier_dev(ref, st), "group barrier")
+        if kind == "bcast":
+            bc_off, bc_bytes = self.bc_regions[1 if channel == 1 else 0]
+            self._in1.value = w.data_ptr()
+            rc = lib.fmpi_bcast_any(ref, self._in1_ref, nbytes, root, bc_off, bc_bytes, self._lp_auto, st)
+            cuda_check(rc, "group bcast")
+        else:
+            ar_off, ar_bytes = self.ar_regions[1 if channel == 1 else 0]
+            es, n = w.element_size(), w.numel()
+            code = _DT[w.dtype]
+            bulk = n if nbytes % 16 == 0 or nbytes <= (200 << 10) else (nbytes // 16 * 16) // es
+            off = 0
+            for cnt in ((bulk, n - bulk) if bulk < n else (bulk,)):
+                if cnt:
+                    self._in1.value = self._out1.value = w.data_ptr() + off * es
+                    if kind == "allreduce":
+                        rc = lib.fmpi_allreduce_any(ref, self._in1_ref, self._out1_ref, cnt, code, op, ar_off,
+                                                    ar_bytes, self._lp_auto, st)
+                    else:
+                        rc = lib.fmpi_reduce_any(ref, self._in1_ref, self._out1_ref, cnt, code, op, root, ar_off,
+                                                 ar_bytes, self._lp_auto, st)
+                    cuda_check(rc, "group " + kind)
+                off += cnt
+        cuda_check(lib.fmpi_barrier_dev(ref, st), "group barrier")
+        _native.launch_count += 3
+        if copy and (kind == "allreduce" or (kind == "reduce") == (group.rank == root)):
+            self._copy_back(t, w)
+        return t
+
+    def allreduce(self, t: torch.Tensor, op: int, launch=None, group=None):
+        if group is not None:
+            return self._group_call("allreduce", t, op, -1, group)
         if self.world == 1 or t.numel() == 0:
             return t
         if self.native:
@@ -536,7 +590,9 @@ class DeviceWorld(_Base):
             self._copy_back(t, w)
         return t
 
-    def reduce(self, t: torch.Tensor, op: int, root: int):
+    def reduce(self, t: torch.Tensor, op: int, root: int, group=None):
+        if group is not None:
+            return self._group_call("reduce", t, op, root, group)
         if self.world == 1 or t.numel() == 0:
             return t
         if self.native:
@@ -556,7 +612,9 @@ class DeviceWorld(_Base):
             self._copy_back(t, w)
         return t
 
-    def bcast(self, t: torch.Tensor, root: int, channel: int = 0, stream=None):
+    def bcast(self, t: torch.Tensor, root: int, channel: int = 0, stream=None, group=None):
+        if group is not None:
+            return self._group_call("bcast", t, 0, root, group, channel, stream)
         if self.world == 1 or t.numel() == 0:
             return t
         if self.native:
@@ -590,8 +648,19 @@ class DeviceWorld(_Base):
             tt.copy_(w.view(torch.bool) if t.dtype == torch.bool else w)
 
     # ------------------------------------------------------------------ non-blocking
-    def allreduce_async(self, send: torch.Tensor, recv: torch.Tensor, op: int) -> torch.cuda.Event:
+    def allreduce_async(self, send: torch.Tensor, recv: torch.Tensor, op: int, group=None) -> torch.cuda.Event:
         ev = torch.cuda.Event()
+        if group is not None:
+            cs = self.comm_stream
+            cs.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(cs):
+                if recv.data_ptr() != send.data_ptr():
+                    recv.copy_(send)
+                self._group_call("allreduce", recv, op, -1, group, 1, cs)
+                for x in (send, recv):
+                    x.record_stream(cs)
+                ev.record(cs)
+            return ev
         if self.world == 1 or send.numel() == 0:
             if recv.data_ptr() != send.data_ptr():
                 recv.copy_(send)
@@ -615,15 +684,15 @@ class DeviceWorld(_Base):
             ev.record(cs)
         return ev
 
-    def bcast_async(self, buf: torch.Tensor, root: int) -> torch.cuda.Event:
+    def bcast_async(self, buf: torch.Tensor, root: int, group=None) -> torch.cuda.Event:
         ev = torch.cuda.Event()
-        if self.world == 1 or buf.numel() == 0:
+        if (self.world == 1 and group is None) or buf.numel() == 0:
             ev.record()
             return ev
         cs = self.comm_stream
         cs.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(cs):
-            self.bcast(buf, root, channel=1, stream=cs)
+            self.bcast(buf, root, channel=1, stream=cs, group=group)
             buf.record_stream(cs)
             ev.record(cs)
         return ev

@@ -224,6 +224,8 @@ def Finalize() -> None:
     if not _S.initialized:
         return
     with _S.lock:
+        from . import group as _group
+        _group.free_all()
         if _S.device_world is not None:
             try:
                 _S.device_world.close()

@@ -92,7 +92,7 @@ torch.cuda.synchronize()
 tri = w * (w + 1) / 2
 assert torch.equal(big_a, torch.full_like(big_a, tri * w ** 3)), big_a[:3]
 assert torch.equal(big_b, torch.full_like(big_b, (w * w) * w ** 3)), big_b[:3]
-assert torch.equal(sm_a, torch.full_like(sm_a, float(w))) and torch.equal(sm_b, torch.full_like(sm_b, 1.0))
+assert torch.equal(sm_a, torch.full_like(sm_a, float(w))) and torch.equal(sm_b, torch.full_like(sm_b, 2.0 * w - 1))
 
 # push-mode kernels (one-shot all-reduce, staged broadcast) on the communication stream while the
 # SMs are busy with somebody else's work: blocks of one launch may start far apart in time and

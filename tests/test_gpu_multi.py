@@ -61,3 +61,20 @@ def test_lost_rank_ends_in_an_error_not_a_spinning_gpu():
     joined = "\n".join(outs)
     assert code == 7, joined
     assert "SURVIVOR_ERROR rank 0" in joined and time.time() - t0 < 90, joined
+
+
+@pytest.mark.skipif(NGPU < 4, reason="rank groups on device tensors need four GPUs")
+def test_rank_groups_on_device_tensors():
+    _run("groups.py", 4, args=("cuda",))
+
+
+def test_selftest_through_the_live_world():
+    """fluxmpi_b200.selftest (what bench.py runs before timing at N >= 2) at the largest world."""
+    from fluxmpi_b200.launch import launch
+    import json, os, sys
+    from conftest import ROOT
+    env = {"PYTHONPATH": str(ROOT) + os.pathsep + os.environ.get("PYTHONPATH", ""), "FMPI_TIMEOUT_S": "60"}
+    code, outs = launch(NGPU, ["fluxmpi_b200.selftest"], module=True, timeout=600, env_extra=env, capture=True)
+    assert code == 0, "\n".join(o[-2000:] for o in outs)
+    rep = json.loads([ln for ln in outs[0].splitlines() if ln.startswith("{")][-1])
+    assert rep["ok"] and rep["cases"] >= 20 and rep["world"] == NGPU, rep

@@ -120,3 +120,10 @@ def test_doctor_passes_on_this_machine(capsys):
     checks = {c["check"]: c["status"] for c in report["checks"]}
     assert checks["libfmpi_host.so"] == "ok" and checks["host world, 2 ranks (shared memory)"] == "ok"
     assert checks["two pretend nodes x 1 rank (TCP mesh)"] == "ok" and not report["failed"]
+
+
+def test_rank_groups_run_different_collectives_concurrently(spmd):
+    """fm.Group: {0,1} and {2,3} at the same time, a 3-of-4 group, then the world (the `comm`
+    argument of /root/reference/src/mpi_extensions.jl:97,119,141)."""
+    outs = spmd("groups.py", 4)
+    assert all(f"RANK_OK {r}" in o for r, o in enumerate(outs))
