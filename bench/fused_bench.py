@@ -6,11 +6,13 @@ flat buffer, against the baseline it replaces (NCCL all-reduce + torch's fused A
 
 Sizes: ResNet-50 (25.6 M fp32), ViT-B/16 (86.6 M fp32), GPT-2 medium (354.8 M bf16 + fp32
 master). Device time, CUDA events, max over ranks; L2 is flushed between iterations
-(`fmpi_flush_l2` writes 256 MB). Roofline per BASELINE.json: the slower of the optimiser's HBM
-bytes at the measured copy bandwidth and the bytes that must cross NVLink at the measured
-770 GB/s per direction:
-  P2P two-shot: in = (W-1)/W * N * es (gradient reads) + (W-1)/W * N * es (parameter stores)
-  NVLS:         in = N/W * es (reduced gradient) + (W-1)/W * N * es (multicast parameters)
+(`fmpi_flush_l2` writes 256 MB). Roofline: the slower of the optimiser's HBM bytes at the measured
+copy bandwidth (MEASURED_PEAKS.json) and the bytes that must cross NVLink per direction per GPU,
+  P2P two-shot: 2 * (W-1)/W * N * es      (gradient slices in, parameter slices in)
+  NVLS:         (W+1)/W * N * es          (N/W reduced gradient + N multicast parameters in;
+                                           N served + N/W stored out)
+divided by the link rate; two fractions are reported: against 900 GB/s (nominal, the figure
+BASELINE.json fixes) and against 770 GB/s (the measured peer-copy rate, B200_PROFILING.md).
 """
 from __future__ import annotations
 
@@ -27,7 +29,17 @@ from fluxmpi_b200 import rules as R                                # noqa: E402
 from fluxmpi_b200.ops import fused as F                            # noqa: E402
 from fluxmpi_b200.parallel.engine import DataParallelEngine        # noqa: E402
 
-HBM_GBS, LINK_GBS = 6540.8, 770.0
+LINK_NOMINAL, LINK_MEASURED = 900.0, 770.0
+
+
+def hbm_gbs() -> float:
+    try:
+        return float(json.loads((Path(__file__).resolve().parent.parent / "MEASURED_PEAKS.json").read_text())["hbm_gbs"])
+    except (OSError, ValueError, KeyError):
+        return 6650.0
+
+
+HBM_GBS = hbm_gbs()
 
 
 class Flat(torch.nn.Module):
@@ -61,9 +73,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default="")
     ap.add_argument("--iters", type=int, default=8)
-    ap.add_argument("--blocks", default="16,48")
+    ap.add_argument("--blocks", default="48,96,128")
     ap.add_argument("--algos", default="twoshot,nvls")
-    ap.add_argument("--models", default="resnet50,vit_b16,gpt2_medium")
+    ap.add_argument("--models", default="mlp,resnet50,vit_b16,gpt2_medium")
     ap.add_argument("--no-baseline", action="store_true")
     a = ap.parse_args()
     fm.Init()
@@ -75,20 +87,24 @@ def main():
         import torch.distributed as dist
         dist.init_process_group("nccl", rank=r, world_size=w, device_id=dev)
     rows = []
-    for name, n, dt in (("resnet50", 25_557_056, torch.float32), ("vit_b16", 86_567_680, torch.float32),
-                        ("gpt2_medium", 354_823_168, torch.bfloat16)):
+    for name, n, dt in (("mlp", 263_744, torch.float32), ("resnet50", 25_557_056, torch.float32),
+                        ("vit_b16", 86_567_680, torch.float32), ("gpt2_medium", 354_823_168, torch.bfloat16)):
         if name not in a.models.split(","):
             continue
         es = 2 if dt == torch.bfloat16 else 4
-        row = {"model": name, "numel": n, "dtype": str(dt).split(".")[-1], "world": w}
-        for algo in ([x for x in a.algos.split(",") if x != "nvls" or dw.has_multicast] if w > 1 else ["twoshot"]):
-            for blocks in ((0,) if w == 1 else tuple(int(b) for b in a.blocks.split(","))):
+        row = {"model": name, "numel": n, "dtype": str(dt).split(".")[-1], "world": w, "bytes": n * es}
+        algos = [x for x in a.algos.split(",") if x != "nvls" or dw.has_multicast] if w > 1 else ["twoshot"]
+        if name == "mlp":
+            algos = [x for x in algos if x != "oneshot"] + (["oneshot"] if w > 1 else [])
+        else:
+            algos = [x for x in algos if x != "oneshot"]
+        for algo in algos:
+            for blocks in ((0,) if (w == 1 or algo == "oneshot") else tuple(int(b) for b in a.blocks.split(","))):
                 mod = Flat(n, dt)
                 eng = DataParallelEngine(mod, R.Adam(1e-3), bucket_mb=1e9, overlap=False, algo=algo,
                                          blocks=blocks, sync_params=False)
                 us = timeit(eng.step, lambda: eng.G.normal_(), a.iters, dev)
-                key = f"ours_{algo}_b{blocks}_us"
-                row[key] = round(us, 1)
+                row[f"ours_{algo}_b{blocks}_us"] = round(us, 1)
                 eng.close()
                 del eng, mod
                 torch.cuda.empty_cache()
@@ -108,20 +124,35 @@ def main():
 
         row["nccl_plus_fused_adam_us"] = None if a.no_baseline else round(timeit(base, lambda: g.normal_(), a.iters, dev), 1)
         hbm_owner = (8 * n * es / 4 + 20 * n / w) if dt == torch.float32 else (n * (2 * es + 2) + 24 * n / w)
-        row["roofline_p2p_us"] = round(max(hbm_owner / HBM_GBS / 1e3, 2 * (w - 1) / w * n * es / LINK_GBS / 1e3), 1)
-        row["roofline_nvls_us"] = round(max(hbm_owner / HBM_GBS / 1e3, n * es / LINK_GBS / 1e3), 1)
-        ours = min(v for k, v in row.items() if k.startswith("ours_"))
-        row["best_ours_us"] = ours
-        row["speedup_vs_nccl_adam"] = None if a.no_baseline else round(row["nccl_plus_fused_adam_us"] / ours, 2)
-        row["fraction_of_roofline"] = round(min(row["roofline_p2p_us"], row["roofline_nvls_us"]) / ours, 3) if w > 1 \
-            else round((32 * n / HBM_GBS / 1e3) / ours, 3)
+        hbm_us = hbm_owner / HBM_GBS / 1e3
+        link = {"p2p": 2 * (w - 1) / w * n * es, "nvls": (w + 1) / w * n * es}
+        ours = {k: v for k, v in row.items() if k.startswith("ours_")}
+        best_key = min(ours, key=ours.get)
+        best = ours[best_key]
+        row["best_ours"] = best_key
+        row["best_ours_us"] = best
+        row["speedup_vs_nccl_adam"] = None if a.no_baseline else round(row["nccl_plus_fused_adam_us"] / best, 2)
+        if w > 1:
+            kind = "nvls" if "_nvls_" in best_key else "p2p"
+            for tag, rate in (("900", LINK_NOMINAL), ("770", LINK_MEASURED)):
+                roof = max(hbm_us, link[kind] / rate / 1e3)
+                row[f"roofline_{kind}_us_at_{tag}"] = round(roof, 1)
+                row[f"fraction_of_roofline_at_{tag}"] = round(roof / best, 3)
+            # the bytes-minimal algorithm on this box is the in-switch one: also quote against it
+            roof = max(hbm_us, link["nvls" if dw.has_multicast else "p2p"] / LINK_NOMINAL / 1e3)
+            row["fraction_of_min_traffic_roofline_at_900"] = round(roof / best, 3)
+        else:
+            row["fraction_of_hbm_roofline"] = round((32 * n / HBM_GBS / 1e3) / best, 3)
         rows.append(row)
         if r == 0:
             print(json.dumps(row), flush=True)
         del p, g, lp, opt
         torch.cuda.empty_cache()
     if r == 0 and a.out:
-        Path(a.out).write_text(json.dumps({"world": w, "rows": rows, "hbm_gbs": HBM_GBS, "link_gbs": LINK_GBS}, indent=1))
+        Path(a.out).parent.mkdir(parents=True, exist_ok=True)
+        Path(a.out).write_text(json.dumps({"world": w, "rows": rows, "hbm_gbs_measured": HBM_GBS,
+                                           "link_gbs_nominal": LINK_NOMINAL, "link_gbs_measured": LINK_MEASURED,
+                                           "timing": "CUDA events, L2 flushed, max over ranks"}, indent=1))
     if dist is not None:
         dist.destroy_process_group()
     fm.Finalize()

@@ -65,6 +65,18 @@ def time_op(fn, bufs, iters, warm, graph=False):
     return float(t)
 
 
+def nccl_registered_pool(dist, dev):
+    """A torch memory pool whose blocks come from ncclMemAlloc and are registered with the
+    communicator (NCCL's user-buffer registration: zero-copy / NVLS on the caller's tensor) — the
+    like-for-like partner of fm.symm_empty. None when this torch / NCCL build has no such API."""
+    try:
+        backend = dist.distributed_c10d._get_default_group()._get_backend(dev)
+        pool = torch.cuda.MemPool(backend.mem_allocator)
+        return backend, pool
+    except Exception as e:                                       # noqa: BLE001
+        return None, f"{type(e).__name__}: {str(e)[:120]}"
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--max-mb", type=float, default=1024)
@@ -74,8 +86,11 @@ def main():
     ap.add_argument("--ops", default="allreduce,bcast,reduce")
     ap.add_argument("--no-nccl", action="store_true")
     ap.add_argument("--graph", action="store_true", help="time CUDA-graph replays (no host launch cost)")
-    ap.add_argument("--symm", action="store_true", help="our buffers come from fm.symm_empty (registered memory)")
+    ap.add_argument("--columns", default="any,symm,nccl,nccl_reg",
+                    help="any = ours on ordinary tensors, symm = ours on fm.symm_empty tensors, "
+                         "nccl = NCCL on ordinary tensors, nccl_reg = NCCL on registered (ncclMemAlloc) tensors")
     a = ap.parse_args()
+    cols = a.columns.split(",")
 
     fm.Init()
     r, w = fm.local_rank(), fm.total_workers()
@@ -85,9 +100,15 @@ def main():
     es = torch.empty((), dtype=dt).element_size()
 
     dist = None
-    if not a.no_nccl and w > 1:
+    reg_backend = reg_pool = None
+    reg_note = ""
+    if not a.no_nccl and w > 1 and ("nccl" in cols or "nccl_reg" in cols):
         import torch.distributed as dist
         dist.init_process_group("nccl", rank=r, world_size=w, device_id=dev)
+        if "nccl_reg" in cols:
+            reg_backend, reg_pool = nccl_registered_pool(dist, dev)
+            if reg_backend is None:
+                reg_note, reg_pool = reg_pool, None
 
     sizes = []
     s = a.min_bytes
@@ -95,22 +116,34 @@ def main():
         sizes.append(s)
         s *= 4
     rows = []
-    symm_pool: dict = {}
     pool_bytes = 192 << 20
+    symm_cache: dict = {}
+    reg_big = []
+    if reg_pool is not None:
+        # two maximum-size tensors from the registered pool, registered once; smaller messages
+        # are slices of them (registration covers the whole allocation)
+        try:
+            with torch.cuda.use_mem_pool(reg_pool):
+                reg_big = [torch.ones(sizes[-1] // es, dtype=dt, device=dev) for _ in range(2)]
+            reg_backend.register_mem_pool(reg_pool)
+        except Exception as e:                                   # noqa: BLE001
+            reg_note, reg_pool, reg_big = f"{type(e).__name__}: {str(e)[:120]}", None, []
     for nbytes in sizes:
         n = nbytes // es
         nbuf = max(1, min(64, pool_bytes // nbytes))
-        if a.symm:      # buffers in symmetric memory: in-place NVLink kernels, no staging copies
-            nbuf = max(1, min(nbuf, 4))
-            if nbytes not in symm_pool:
-                symm_pool[nbytes] = [fm.symm_empty(n, dt) for _ in range(nbuf)]
-            bufs = symm_pool[nbytes]
-            for b in bufs:
-                b.fill_(1)
-        else:
-            bufs = [torch.ones(n, dtype=dt, device=dev) for _ in range(nbuf)]
         iters = 200 if nbytes <= (1 << 20) else 40 if nbytes <= (64 << 20) else 10
         warm = max(3, iters // 10)
+        sets = {}
+        if "any" in cols or "nccl" in cols:
+            sets["ordinary"] = [torch.ones(n, dtype=dt, device=dev) for _ in range(nbuf)]
+        if "symm" in cols and dw.native:
+            k = max(1, min(nbuf, 4))
+            if nbytes not in symm_cache:
+                symm_cache[nbytes] = [fm.symm_empty(n, dt) for _ in range(k)]
+            sets["symm"] = symm_cache[nbytes]
+        if reg_big:
+            per = max(1, min(nbuf // 2, reg_big[0].numel() // n))
+            sets["nccl_reg"] = [big[i * n:(i + 1) * n] for big in reg_big for i in range(per)]
         row = {"bytes": nbytes, "world": w}
         for op in a.ops.split(","):
             if op == "allreduce":
@@ -125,27 +158,34 @@ def main():
                 ours = lambda b: fm.reduce_(b, "sum", 0)
                 nccl = (lambda b: dist.reduce(b, 0)) if dist else None
                 factor = 1.0
-            ms = time_op(ours, bufs, iters, warm, a.graph)
-            row[f"{op}_us"] = round(ms * 1e3, 2)
-            row[f"{op}_busbw_gbs"] = round(nbytes / (ms * 1e-3) * factor / 1e9, 2)
-            if nccl is not None:
+            plan = [("any", ours, "ordinary"), ("symm", ours, "symm"), ("nccl", nccl, "ordinary"),
+                    ("nccl_reg", nccl, "nccl_reg")]
+            for col, fn, key in plan:
+                if col not in cols or fn is None or key not in sets:
+                    continue
+                bufs = sets[key]
                 for b in bufs:
                     b.fill_(1)
-                msn = time_op(nccl, bufs, iters, warm, a.graph)
-                row[f"{op}_nccl_us"] = round(msn * 1e3, 2)
-                row[f"{op}_nccl_busbw_gbs"] = round(nbytes / (msn * 1e-3) * factor / 1e9, 2)
-                row[f"{op}_speedup"] = round(msn / ms, 3)
-            for b in bufs:
-                b.fill_(1)
+                ms = time_op(fn, bufs, iters, warm, a.graph)
+                row[f"{op}_{col}_us"] = round(ms * 1e3, 2)
+                row[f"{op}_{col}_busbw_gbs"] = round(nbytes / (ms * 1e-3) * factor / 1e9, 2)
+            best_nccl = min((row[f"{op}_{c}_us"] for c in ("nccl", "nccl_reg") if f"{op}_{c}_us" in row), default=None)
+            if best_nccl is not None:
+                for col in ("any", "symm"):
+                    if f"{op}_{col}_us" in row:
+                        row[f"{op}_{col}_speedup"] = round(best_nccl / row[f"{op}_{col}_us"], 3)
         rows.append(row)
         if r == 0:
             print(json.dumps(row), flush=True)
-        del bufs
+        sets.clear()
         torch.cuda.empty_cache()
     if r == 0 and a.out:
         Path(a.out).parent.mkdir(parents=True, exist_ok=True)
         Path(a.out).write_text(json.dumps({
             "world": w, "dtype": a.dtype, "mode": dw.mode, "multicast": dw.has_multicast,
+            "nccl_registered": "ncclMemAlloc pool registered with the communicator" if reg_pool is not None
+            else f"unavailable ({reg_note})" if reg_note else "not requested",
+            "speedup": "NCCL's best column (ordinary or registered) time / ours",
             "timing": "CUDA events, max over ranks" + (", CUDA-graph replay" if a.graph else ", eager launches"),
             "rows": rows}, indent=1))
     if dist:

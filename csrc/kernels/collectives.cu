@@ -573,12 +573,12 @@ pipe_kernel(fmpi_devcomm c, PipeArgs a) {
   uint8_t* dst = static_cast<uint8_t*>(a.out.p[ai]);
   uint32_t* pad = x.my_pad;
   __shared__ uint32_t base_s[kPipeSlots];
-  __shared__ uint32_t last_s;
   if (threadIdx.x < kPipeSlots) base_s[threadIdx.x] = pad[kCtlBase + kCtlPipeBase + threadIdx.x];
   // every rank has entered this call => every rank has left the previous one on this channel
   block_barrier(x, c);
 
   // ---- roles (the grid is the same on every rank; what a copy CTA does depends on the rank)
+  const bool direct = a.kind == 2 && a.n_link == 0;   // broadcast without the re-emit step
   const bool has_in = a.kind != 2 || me == a.root;
   const bool has_out = a.kind == 0 || (a.kind == 1 ? me == a.root : me != a.root);
   const int n_in = has_in ? (has_out ? a.n_copy / 2 : a.n_copy) : 0;
@@ -605,17 +605,17 @@ pipe_kernel(fmpi_devcomm c, PipeArgs a) {
     __syncthreads();
   };
   // this CTA is done with its share of the slot; the CTA that completes the count tells the peers
+  // (one sys-scope release fence per CTA and chunk: it orders this CTA's data stores — the
+  // __syncthreads before it makes them this thread's predecessors — before the counter; the CTA
+  // that completes the count then publishes the flag to every peer with release stores)
   auto done = [&](int rl, int s, uint32_t total, uint32_t value) {
     __syncthreads();
     if (threadIdx.x == 0) {
       fence_acq_rel_sys();
-      last_s = atomicAdd(counter(rl, s), 1u) + 1 == total;
-      fence_acq_rel_sys();
-    }
-    __syncthreads();
-    if (last_s && int(threadIdx.x) < W) {
-      fence_acq_rel_sys();
-      st_release_sys(flag_of(threadIdx.x, rl, s, me), value);
+      if (atomicAdd(counter(rl, s), 1u) + 1 == total) {
+        fence_acq_rel_sys();
+        for (int r = 0; r < W; ++r) st_release_sys(flag_of(r, rl, s, me), value);
+      }
     }
   };
 
@@ -644,8 +644,19 @@ pipe_kernel(fmpi_devcomm c, PipeArgs a) {
         }
         if (a.kind != 2) {
           uint8_t* slot = byte_ptr(c.data[me], soff);
-          vec_loop<4>(0, cv, t0, stride, [&](uint64_t j) { return ld_stream(src + (v0 + j) * 16); },
+          vec_loop<8>(0, cv, t0, stride, [&](uint64_t j) { return ld_stream(src + (v0 + j) * 16); },
                       [&](uint64_t j, uint4 v) { *reinterpret_cast<uint4*>(slot + j * 16) = v; });
+        } else if (direct) {                  // the root sends the whole chunk to every receiver
+          if (kNvls) {
+            uint8_t* mc = byte_ptr(c.mc_data, soff);
+            vec_loop<8>(0, cv, t0, stride, [&](uint64_t j) { return ld_stream(src + (v0 + j) * 16); },
+                        [&](uint64_t j, uint4 v) { multimem_st(mc + j * 16, v); });
+          } else {
+            vec_loop<8>(0, cv, t0, stride, [&](uint64_t j) { return ld_stream(src + (v0 + j) * 16); },
+                        [&](uint64_t j, uint4 v) {
+                          store_to_ranks(c, -1, me, [&](int r) { return byte_ptr(c.data[r], soff) + j * 16; }, v);
+                        });
+          }
         } else {
           for (int dq = 0; dq < W; ++dq) {    // the root scatters: slice q -> rank q's slot
             const int q = (me + dq) % W;
@@ -691,9 +702,10 @@ pipe_kernel(fmpi_devcomm c, PipeArgs a) {
         }
         done(kPipeLink, s, uint32_t(a.n_link) * (u + 1), U);
       } else {
-        wait_peers(kPipeLink, s, U, -1, -1);
+        if (direct) wait_peers(kPipeIn, s, U, a.root, -1);
+        else wait_peers(kPipeLink, s, U, -1, -1);
         const uint8_t* slot = byte_ptr(c.data[me], soff);
-        vec_loop<4>(0, cv, t0, stride, [&](uint64_t j) { return ld_volatile(slot + j * 16); },
+        vec_loop<8>(0, cv, t0, stride, [&](uint64_t j) { return ld_volatile(slot + j * 16); },
                     [&](uint64_t j, uint4 v) { st_stream(dst + (v0 + j) * 16, v); });
         done(kPipeOut, s, uint32_t(n_out) * (u + 1), U);
       }
@@ -810,10 +822,10 @@ const PipeCfg& pipe_cfg();
 bool pipe_wanted(const fmpi_devcomm* c, int algo, uint64_t nbytes, int kind);
 
 // The tail of every staging region belongs to the pipelined kernels (at most a quarter of it,
-// at most 32 MB): their slots are read and written by peers outside the other families' barriers.
+// at most 48 MB): their slots are read and written by peers outside the other families' barriers.
 uint64_t pipe_carve(uint64_t stage_bytes) {
   uint64_t p = stage_bytes / 4;
-  if (p > (32ull << 20)) p = 32ull << 20;
+  if (p > (48ull << 20)) p = 48ull << 20;
   return p & ~uint64_t(255);
 }
 
@@ -924,19 +936,22 @@ int reduce_any_impl(const fmpi_devcomm* c, const void* const* in, void* const* o
 }
 
 // ---- chunk pipeline: launch parameters (env overrides exist for the tuning runs only)
-struct PipeCfg { int link_nvls, link_p2p, copy_nvls, copy_p2p, slots; uint64_t chunk_bytes, min_ar, min_other; };
+struct PipeCfg { int link_nvls, link_p2p, copy_nvls, copy_p2p, slots, nvls_min_world; uint64_t chunk_bytes, min_ar, min_other; };
 const PipeCfg& pipe_cfg() {
   static const PipeCfg cfg = [] {
     auto env = [](const char* k, long d) { const char* v = getenv(k); return v && *v ? atol(v) : d; };
     PipeCfg p;
     p.link_nvls = int(env("FMPI_PIPE_LINK_NVLS", 16));
     p.link_p2p = int(env("FMPI_PIPE_LINK_P2P", 64));
-    p.copy_nvls = int(env("FMPI_PIPE_COPY_NVLS", 48));
-    p.copy_p2p = int(env("FMPI_PIPE_COPY_P2P", 64));
+    p.copy_nvls = int(env("FMPI_PIPE_COPY_NVLS", 64));
+    p.copy_p2p = int(env("FMPI_PIPE_COPY_P2P", 80));
     p.slots = int(env("FMPI_PIPE_SLOTS", 3));
     if (p.slots < 2) p.slots = 2;
     if (p.slots > kPipeSlots) p.slots = kPipeSlots;
-    p.chunk_bytes = uint64_t(env("FMPI_PIPE_CHUNK_KB", 8192)) << 10;
+    // the in-switch link phase moves (W+1)/W * N per direction against 2(W-1)/W * N for the
+    // peer-to-peer one: a win from four ranks up only
+    p.nvls_min_world = int(env("FMPI_PIPE_NVLS_MIN_WORLD", 4));
+    p.chunk_bytes = uint64_t(env("FMPI_PIPE_CHUNK_KB", 16384)) << 10;
     p.min_ar = uint64_t(env("FMPI_PIPE_MIN_AR_KB", 48 << 10)) << 10;
     p.min_other = uint64_t(env("FMPI_PIPE_MIN_KB", 8 << 10)) << 10;
     return p;
@@ -959,13 +974,19 @@ int pipe_impl(const fmpi_devcomm* c, const void* const* in, void* const* out, ui
               int op, int kind, int root, uint64_t stage_off, uint64_t stage_bytes, const fmpi_launch* l,
               cudaStream_t st) {
   const PipeCfg& cfg = pipe_cfg();
-  const bool nvls = kind == 2 ? (c->mc_data && !c->emulate) : nvls_capable(c, dtype, op);
+  const bool forced = l && l->algo == FMPI_ALGO_NVLS;
+  const bool nvls = (kind == 2 ? (c->mc_data && !c->emulate && c->world > 1) : nvls_capable(c, dtype, op)) &&
+                    (forced || c->world >= cfg.nvls_min_world);
   PipeArgs a{};
   a.in = table(in, c);
   a.out = table(reinterpret_cast<const void* const*>(out), c);
   a.nvec = nvec; a.kind = kind; a.root = root; a.op = op; a.stage_off = stage_off;
   a.nslots = cfg.slots;
-  uint64_t chunk = cfg.chunk_bytes;
+  // chunks: large enough that the per-chunk hand-over (a few microseconds) stays small, small
+  // enough that the pipeline fills quickly: about 1/12 of the message, 1 MB .. chunk_bytes
+  uint64_t chunk = nvec * 16 / 12;
+  if (chunk < (1ull << 20)) chunk = 1ull << 20;
+  if (chunk > cfg.chunk_bytes) chunk = cfg.chunk_bytes;
   if (chunk * a.nslots > stage_bytes) chunk = stage_bytes / a.nslots;
   a.chunk_vec = chunk / 16 / c->world * c->world;
   if (a.chunk_vec < uint64_t(c->world)) return set_error("pipeline staging area too small");
@@ -980,6 +1001,7 @@ int pipe_impl(const fmpi_devcomm* c, const void* const* in, void* const* out, ui
   if (c->emulate) cap = 128 / c->world;
   if (total > cap) { a.n_link = a.n_link * cap / total; total = cap; }
   if (a.n_link < 1) a.n_link = 1;
+  if (kind == 2 && c->world <= 2) a.n_link = 0;     // nobody to re-emit to: the root sends directly
   if (total - a.n_link < 2) total = a.n_link + 2;
   a.n_copy = total - a.n_link;
   int threads = (l && l->threads > 0 && l->threads <= 512) ? (l->threads + 31) / 32 * 32 : 512;

@@ -39,7 +39,7 @@ constexpr int kPipeFlagWords = 3 * kPipeSlots * FMPI_MAX_RANKS;
 constexpr int kChannelWords = kFlagWords + 2 * FMPI_MAX_BLOCKS + kPipeFlagWords;
 constexpr size_t kSigPadBytes = size_t(FMPI_NUM_CHANNELS) * kChannelWords * sizeof(uint32_t);
 constexpr int kCtlBase = kFlagWords + FMPI_MAX_BLOCKS;
-constexpr int kCtlSeq = 0, kCtlTicket = 1;
+constexpr int kCtlSeq = 0, kCtlTicket = 1, kCtlGrid = 2;   // kCtlGrid: local grid-wide barrier counter
 constexpr int kCtlPipeBase = 8;                      // [kPipeSlots] slot uses in earlier calls
 constexpr int kCtlPipeCnt = kCtlPipeBase + kPipeSlots;  // [3 roles][kPipeSlots] local counters
 constexpr int kPipeFlagBase = kFlagWords + 2 * FMPI_MAX_BLOCKS;

@@ -452,7 +452,9 @@ int fmpi_fused_step(const fmpi_devcomm* c, uint64_t g_off, int gdt, uint64_t p_o
     // kernel wants more CTAs than a pure all-reduce (measured at 8 GPUs, ResNet-50-sized
     // bucket, NVLS: 16 CTAs 454 us, 48: 301 us, 96: 286 us, 148: 289 us)
     // (round 2 kernel: the in-switch flavour fits two CTAs per SM; 128 of them by default)
-    const uint64_t cap = c->world == 1 ? 148 * 4 : nvls ? 128 : 96;
+    // measured at 2 GPUs (102 MB, peer-to-peer flavour): 48 CTAs 440 us, 128 CTAs 211 us — the
+    // owner needs the whole chip's load slots to keep W remote vectors per element in flight
+    const uint64_t cap = c->world == 1 ? 148 * 4 : nvls ? 128 : 144;
     blocks = int(want < 1 ? 1 : want > cap ? cap : want);
   }
   if (c->world > 1 && blocks > FMPI_MAX_BLOCKS) blocks = FMPI_MAX_BLOCKS;

@@ -29,6 +29,7 @@ CUDA_SOURCES = [
     "kernels/collectives.cu",
     "kernels/fused_step.cu",
     "kernels/multi_tensor.cu",
+    "kernels/tree_step.cu",
     "kernels/reduce_diag.cu",
     "kernels/batchnorm.cu",
     "kernels/pool.cu",

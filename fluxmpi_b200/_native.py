@@ -219,6 +219,8 @@ def cuda():
         lib.fmpi_step_advance.argtypes = [vp, vp]
         lib.fmpi_multi_tensor_step.argtypes = [i32, vp, vp, vp, vp, vp, i32, i32,
                                                C.POINTER(Hyper), C.c_int64, vp]
+        lib.fmpi_tree_step_oneshot.argtypes = [dc, i32, vp, u64, i32, C.POINTER(Hyper), C.c_int64, u64, u64, lp, vp]
+        lib.fmpi_tree_allreduce.argtypes = [dc, i32, vp, u64, u64, i32, i32, lp, vp]
         lib.fmpi_pack.argtypes = [i32, vp, vp, vp, vp, vp]
         lib.fmpi_unpack.argtypes = [i32, vp, vp, vp, vp, vp]
         lib.fmpi_reduce_scratch_bytes.restype = C.c_size_t

@@ -179,11 +179,10 @@ def _rule_state_tensors(rule, state):
     return mt, vt, max(step, 0), (lambda: wrap((mt, vt, (bt[0] * adam.beta[0], bt[1] * adam.beta[1]))))
 
 
-def try_tree_step_(state_tree, params, grads) -> bool:
-    """One-kernel in-place optimiser step for a whole tree of CUDA leaves
-    (``Optimisers.update!`` semantics): returns False — having changed nothing — when any leaf
-    does not qualify (mixed rules or dtypes, CPU tensors, non-contiguous storage, fp64, a rule
-    without a fused kernel); the caller then walks the tree leaf by leaf."""
+def _collect_tree(state_tree, params, grads):
+    """The leaves of a whole-tree step as flat lists, or None when any leaf does not qualify for
+    the pointer-table kernels (mixed rules or dtypes, CPU tensors, non-contiguous storage, fp64,
+    a rule without a fused kernel). Ties are visited once."""
     from .. import tree as T
     triples, seen = [], set()
 
@@ -206,35 +205,46 @@ def try_tree_step_(state_tree, params, grads) -> bool:
         return all(walk(a, b, c) for a, b, c in zip(cs, cp, cg))
 
     if not walk(state_tree, params, grads) or not triples:
-        return False
+        return None
     rule = triples[0][0].rule
     h = hyper_for(rule)
     if h is None:
-        return False
+        return None
     dt = triples[0][1].dtype
     if dt not in (torch.float32, torch.bfloat16, torch.float16):
-        return False
+        return None
     ms, vs, ps, gs, rebuilds, step = [], [], [], [], [], None
     for leaf, p, g in triples:
         if leaf.rule != rule or not (isinstance(p, torch.Tensor) and isinstance(g, torch.Tensor)):
-            return False
+            return None
         pd, gd = (p.detach() if p.requires_grad else p), (g.detach() if g.requires_grad else g)
         if not (pd.is_cuda and gd.is_cuda and pd.dtype == dt and gd.dtype == dt and pd.is_contiguous()
                 and gd.is_contiguous() and pd.shape == gd.shape and pd.numel() > 0):
-            return False
+            return None
         got = _rule_state_tensors(rule, leaf.state)
         if got is None:
-            return False
+            return None
         m, v, s, rebuild = got
         for t in (m, v):
             if t is not None and not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()
                                       and t.shape == pd.shape):
-                return False
+                return None
         if step is None:
             step = s
         elif s != step:
-            return False
+            return None
         ps.append(pd); gs.append(gd); ms.append(m); vs.append(v); rebuilds.append(rebuild)
+    return rule, h, dt, ps, gs, ms, vs, rebuilds, step or 0, triples
+
+
+def try_tree_step_(state_tree, params, grads) -> bool:
+    """One-kernel in-place optimiser step for a whole tree of CUDA leaves
+    (``Optimisers.update!`` semantics): returns False — having changed nothing — when any leaf
+    does not qualify; the caller then walks the tree leaf by leaf."""
+    got = _collect_tree(state_tree, params, grads)
+    if got is None:
+        return False
+    rule, h, dt, ps, gs, ms, vs, rebuilds, step, triples = got
     need_m, need_v = rule_needs(h)
     key = tuple(t.data_ptr() for t in ps + gs) + tuple(t.data_ptr() for t in ms + vs if t is not None)
     table = _table_cache.get(key)
@@ -244,7 +254,89 @@ def try_tree_step_(state_tree, params, grads) -> bool:
         table = TensorTable(ps, gs, ms if need_m else None, vs if need_v else None)
         _table_cache[key] = table
     # (averaging, if asked for, has already been applied to the gradients by the caller)
-    multi_tensor_step(table, h, step or 0, dt)
+    multi_tensor_step(table, h, step, dt)
     for (leaf, _, _), rebuild in zip(triples, rebuilds):
         leaf.state = rebuild()
     return True
+
+
+# ------------------------------------------------------------------------------ distributed trees
+class TreeTable:
+    """Device table [p | g | m | v | numel | flat offset] for the tree kernels
+    (csrc/kernels/tree_step.cu); flat offsets are 16-byte aligned."""
+
+    def __init__(self, ps, gs, ms, vs):
+        n = len(ps)
+        es = ps[0].element_size()
+        offs, total = [], 0
+        for t in ps:
+            offs.append(total)
+            total += (t.numel() * es + 15) // 16 * 16
+        zeros = [0] * n
+        rows = [[t.data_ptr() for t in ps], [t.data_ptr() for t in gs],
+                [t.data_ptr() for t in ms] if ms is not None else zeros,
+                [t.data_ptr() for t in vs] if vs is not None else zeros,
+                [t.numel() for t in ps], offs]
+        self.n, self.total, self.offs = n, total, offs
+        self.dev = torch.tensor([x for row in rows for x in row], dtype=torch.int64).pin_memory().to(
+            ps[0].device, non_blocking=True)
+        self.keep = (list(ps), list(gs), list(ms or []), list(vs or []))
+        self.ptr = C.c_void_p(self.dev.data_ptr())
+        self.ref = C.byref(self.ptr)
+        self.arena_table = None          # TensorTable whose gradients point into the pack arena
+
+
+_tree_cache: dict = {}
+
+
+def try_tree_step_distributed_(state_tree, params, grads, average: bool) -> bool:
+    """``update!`` through a DistributedOptimizer over CUDA leaves on a native multi-GPU world in
+    at most TWO launches: small trees in ONE (push + barrier + rank-ordered sum + rule applied to
+    the scattered leaves; the reduced gradient never exists in memory), larger trees as
+    gather-and-all-reduce into the symmetric arena + the pointer-table rule kernel reading it.
+    Returns False, having done nothing, when the tree or the world does not qualify."""
+    from .. import runtime
+    S = runtime.state()
+    dw = S.device_world
+    if dw is None or not dw.native or S.world < 2:
+        return False
+    got = _collect_tree(state_tree, params, grads)
+    if got is None:
+        return False
+    rule, h, dt, ps, gs, ms, vs, rebuilds, step, triples = got
+    need_m, need_v = rule_needs(h)
+    key = tuple(t.data_ptr() for t in ps + gs) + tuple(t.data_ptr() for t in ms + vs if t is not None)
+    tab = _tree_cache.get(key)
+    if tab is None:
+        if len(_tree_cache) > 16:
+            _tree_cache.clear()
+        tab = TreeTable(ps, gs, ms if need_m else None, vs if need_v else None)
+        _tree_cache[key] = tab
+    h.grad_scale = 1.0 / S.world if average else 1.0
+    lib = dw._lib
+    dw.check_health()
+    st = _stream_ptr()
+    code = _dtype_code(dt)
+    tr_off, tr_bytes = dw.tree_region
+    slot = (tr_bytes // (2 * S.world)) & ~15
+    if tab.total <= min(slot, int(TREE_ONESHOT_MAX)):
+        cuda_check(lib.fmpi_tree_step_oneshot(dw._comm_refs[0], tab.n, tab.ref, tab.total, code, C.byref(h), step,
+                                              tr_off, tr_bytes, dw._lp_auto, st), "tree_step_oneshot")
+        _native.count_launch()
+    else:
+        arena, refs, off = dw.pack_arena(tab.total)
+        cuda_check(lib.fmpi_tree_allreduce(refs[0], tab.n, tab.ref, off, tab.total, code, _native.SUM,
+                                           dw._lp_auto, st), "tree_allreduce")
+        _native.count_launch()
+        if tab.arena_table is None or tab.arena_table.arena_ptr != arena.data_ptr():
+            es = ps[0].element_size()
+            views = [arena[o:o + p.numel() * es].view(dt).view(p.shape) for o, p in zip(tab.offs, ps)]
+            tab.arena_table = TensorTable(ps, views, ms if need_m else None, vs if need_v else None)
+            tab.arena_table.arena_ptr = arena.data_ptr()
+        multi_tensor_step(tab.arena_table, h, step, dt)
+    for (leaf, _, _), rebuild in zip(triples, rebuilds):
+        leaf.state = rebuild()
+    return True
+
+
+TREE_ONESHOT_MAX = 4 << 20     # bytes; above it the two-launch path moves fewer bytes per link

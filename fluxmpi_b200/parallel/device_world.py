@@ -104,6 +104,7 @@ class DeviceWorld(_Base):
     # may overlap, so they must not share slots); the engine's channel 2 needs no staging
     AR_STAGE_MB = (int(os.environ.get("FMPI_AR_STAGE_MB", 160)), int(os.environ.get("FMPI_AR_ASYNC_STAGE_MB", 64)))
     BCAST_STAGE_MB = (int(os.environ.get("FMPI_BCAST_STAGE_MB", 96)), int(os.environ.get("FMPI_BCAST_ASYNC_STAGE_MB", 32)))
+    TREE_SLOT_MB = 4
     MAX_COMMS = 8            # signal-pad sets: 0 = the world, 1.. = rank groups (fm.Group)
 
     def __init__(self, rank: int, world: int, device: int, job: str):
@@ -293,6 +294,10 @@ class DeviceWorld(_Base):
         for mb in self.BCAST_STAGE_MB:
             self.bc_regions.append((off, mb * MB))
             off += mb * MB
+        # push slots of the one-launch tree step (ops/fused.py): [2 parities][W][4 MB], private to
+        # that kernel family because peers write into them without a handshake
+        self.tree_region = (off, 2 * self.world * self.TREE_SLOT_MB * MB)
+        off += self.tree_region[1]
         self._window_bytes = off
         self.ar_off, self.ar_bytes = self.ar_regions[0]
         self.bc_off, self.bc_bytes = self.bc_regions[0]
@@ -322,6 +327,7 @@ class DeviceWorld(_Base):
                 need = self.sig_bytes + 4 * MB
                 self.ar_regions = [(0, MB), (MB, MB)]
                 self.bc_regions = [(2 * MB, MB), (3 * MB, MB)]
+                self.tree_region = (0, 0)
                 self.ar_off, self.ar_bytes = self.ar_regions[0]
                 self.bc_off, self.bc_bytes = self.bc_regions[0]
             self.base = self.alloc_segment(need)
@@ -727,6 +733,16 @@ class DeviceWorld(_Base):
         self._tables[key] = entry
         return entry
 
+    def pack_arena(self, nbytes: int):
+        """(uint8 tensor of >= nbytes in symmetric memory, comm refs of its segment, byte offset of
+        the tensor in that segment) — the target of the tree-level gather kernels. Collective the
+        first time (and whenever it has to grow): every rank walks the same tree."""
+        need = _align(max(nbytes, 16), 256)
+        if self._pack_arena is None or self._pack_arena.numel() < need:
+            self._pack_arena = self.symm_empty((max(need, 64 * MB),), torch.uint8)
+        refs, off, _ = self.find_symmetric(self._pack_arena)
+        return self._pack_arena, refs, off
+
     def _pack(self, ts, unpack: bool):
         lib = _native.cuda()
         dev, flat, total, n = self._table(ts)
@@ -742,6 +758,32 @@ class DeviceWorld(_Base):
         if any(not t.is_contiguous() for t in ts):
             for t in ts:
                 self.allreduce(t, op)
+            return
+        if (self.native and self.world > 1 and ts[0].dtype in (torch.float32, torch.bfloat16, torch.float16)
+                and all(t.dtype == ts[0].dtype for t in ts)):
+            # two launches: gather the leaves into the symmetric arena and all-reduce it in place
+            # (csrc/kernels/tree_step.cu), then scatter the result back into the leaves
+            from ..ops import fused as _F
+            self.check_health()
+            key = ("tree",) + tuple((t.data_ptr(), t.numel()) for t in ts)
+            tab = self._tables.get(key)
+            if tab is None:
+                if len(self._tables) > 64:
+                    self._tables.clear()
+                tab = _F.TreeTable(ts, ts, None, None)
+                self._tables[key] = tab
+            arena, refs, off = self.pack_arena(tab.total)
+            cuda_check(self._lib.fmpi_tree_allreduce(refs[0], tab.n, tab.ref, off, tab.total, _DT[ts[0].dtype], op,
+                                                     self._lp_auto, _stream_ptr()), "tree_allreduce")
+            _native.count_launch()
+            if getattr(tab, "unpack_tab", None) is None or tab.unpack_arena != arena.data_ptr():
+                es = ts[0].element_size()
+                tab.unpack_tab = torch.tensor([t.data_ptr() for t in ts] + tab.offs + [t.numel() * es for t in ts],
+                                              dtype=torch.int64).pin_memory().to(self.device, non_blocking=True)
+                tab.unpack_arena = arena.data_ptr()
+            b, n = tab.unpack_tab.data_ptr(), tab.n
+            cuda_check(self._lib.fmpi_unpack(n, b, b + 8 * n, b + 16 * n, arena.data_ptr(), _stream_ptr()), "unpack")
+            _native.count_launch()
             return
         flat, total = self._pack(ts, unpack=False)
         view = flat[:total].view(ts[0].dtype if ts[0].dtype != torch.bool else torch.uint8)
@@ -919,4 +961,21 @@ class EmulatedWorld(_Base):
                                                arr(master), lo, hi, C.byref(hyper), arr(step_dev), stage_off,
                                                stage_bytes, self._launch(blocks), _stream_ptr()),
                    "emulated fused_step_oneshot")
+        _native.count_launch()
+
+    def tree_step_oneshot(self, tabs, n: int, total: int, dtype: torch.dtype, hyper, step: int,
+                          stage_off: int, stage_bytes: int, blocks: int = 0, channel: int = 0):
+        """``tabs``: one device table per virtual rank ([p | g | m | v | numel | off] int64)."""
+        lib = _native.cuda()
+        cuda_check(lib.fmpi_tree_step_oneshot(C.byref(self.comms[channel]), n, self._ptrs(tabs), total,
+                                              _dtype_code(dtype), C.byref(hyper), step, stage_off, stage_bytes,
+                                              self._launch(blocks), _stream_ptr()), "emulated tree_step_oneshot")
+        _native.count_launch()
+
+    def tree_allreduce(self, tabs, n: int, off: int, total: int, dtype: torch.dtype, op: int, blocks: int = 0,
+                       channel: int = 0):
+        lib = _native.cuda()
+        cuda_check(lib.fmpi_tree_allreduce(C.byref(self.comms[channel]), n, self._ptrs(tabs), off, total,
+                                           _dtype_code(dtype), op, self._launch(blocks, 0, _native.ALGO_TWOSHOT),
+                                           _stream_ptr()), "emulated tree_allreduce")
         _native.count_launch()

@@ -188,7 +188,7 @@ class DataParallelEngine:
         # kernel also streams m, v and p through HBM; measured at 8 GPUs (bench/fused_bench.py)
         # 48 CTAs are 1.5-1.9x faster than 16 for both variants, so default well above that
         if blocks == 0 and self.world > 1 and self.native:
-            self.blocks = int(os.environ.get("FMPI_FUSED_BLOCKS", 96))
+            self.blocks = int(os.environ.get("FMPI_FUSED_BLOCKS", 0))     # 0: the library's default
         self.algo = _native.ALGO_NVLS if use_nvls else _native.ALGO_TWOSHOT
         if self.oneshot:
             self.algo = _native.ALGO_ONESHOT

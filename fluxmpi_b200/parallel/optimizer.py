@@ -62,6 +62,17 @@ class DistributedOptimizer(R.AbstractRule):
 
     # whole-tree step: one fused gradient reduction, then the inner rule per leaf
     def tree_update(self, state_tree, params, grads, inplace: bool):
+        # CUDA leaves + a rule with a fused kernel on a native multi-GPU world: at most two launches
+        # for the whole step (ops/fused.py try_tree_step_distributed_); `update` runs it on copies
+        if R._any_cuda(params):
+            from ..ops import fused
+            if inplace:
+                if fused.try_tree_step_distributed_(state_tree, params, grads, self.average):
+                    return state_tree, params
+            elif fused.hyper_for(self.optimizer) is not None and runtime.total_workers() > 1:
+                new_st, new_ps = R._copy_for_step(state_tree, params)
+                if fused.try_tree_step_distributed_(new_st, new_ps, grads, self.average):
+                    return new_st, new_ps
         grads = allreduce_gradients(grads)
         if self.average:
             w = runtime.total_workers()

@@ -297,6 +297,25 @@ int fmpi_multi_tensor_step(int n, void* const* p, const void* const* g, float* c
                            float* const* v, const uint64_t* numel, int pdt, int gdt,
                            const fmpi_hyper* h, int64_t step, fmpi_stream st);
 
+/* ---- tree-level fused kernels (csrc/kernels/tree_step.cu): the functional API on leaves that
+ * live wherever autodiff put them (replaces /root/reference/src/optimizer.jl:20-23 and :45-65).
+ * `tables` is a per-emulated-rank array (real mode: entry [0]) of DEVICE pointers to
+ * uint64 [p[n] | g[n] | m[n] | v[n] | numel[n] | flat_offset_bytes[n]] (offsets 16-byte aligned;
+ * m / v entries may be 0 when the rule has no such state). Leaves share one dtype
+ * (f32 / bf16 / f16); moments are fp32.
+ *   fmpi_tree_step_oneshot  ONE launch: push the gradient leaves into the peers' slots
+ *       ([2 parities][world][slot] at stage_off, slot = stage_bytes / (2 * world) >= total_bytes),
+ *       one barrier, rank-ordered sum + rule applied in place to p / m / v. `step` = completed
+ *       steps (bias correction uses step + 1). The reduced gradient never exists in memory.
+ *   fmpi_tree_allreduce     gather the gradient leaves into the symmetric window at `off` and
+ *       all-reduce that region in place (two-shot peer-to-peer or in-switch), one launch; follow
+ *       it with fmpi_multi_tensor_step / fmpi_unpack reading the region through a pointer table. */
+int fmpi_tree_step_oneshot(const fmpi_devcomm* c, int n, const void* const* tables, uint64_t total_bytes,
+                           int dtype, const fmpi_hyper* h, int64_t step, uint64_t stage_off,
+                           uint64_t stage_bytes, const fmpi_launch* l, fmpi_stream st);
+int fmpi_tree_allreduce(const fmpi_devcomm* c, int n, const void* const* tables, uint64_t off,
+                        uint64_t total_bytes, int dtype, int op, const fmpi_launch* l, fmpi_stream st);
+
 /* ---- pack / unpack scattered leaves into / out of a flat buffer (pointer-table kernels) */
 int fmpi_pack(int n, const void* const* src, const uint64_t* offsets_bytes,
               const uint64_t* nbytes, void* flat, fmpi_stream st);

@@ -79,6 +79,60 @@ def run(algo, overlap, bucket_mb, graph=False):
     eng.close()
 
 
+def functional_vs_engine(rule, big: bool):
+    """The reference's loop shape — `Optimisers.update!(state, params, grads)` through a
+    DistributedOptimizer on scattered leaves (src/optimizer.jl:20-23) — must take at most two
+    launches per step and give the engine's bits: same kernels' arithmetic, same rank order."""
+    from fluxmpi_b200 import _native
+    torch.manual_seed(77)
+    shapes = [(256, 128), (128,), (33, 7), (1,)] + ([(1 << 21,), (3000, 700)] if big else [])
+    ps = {f"p{i}": torch.randn(s, device=dev) for i, s in enumerate(shapes)}
+    mod = torch.nn.ParameterDict({k: torch.nn.Parameter(v.clone()) for k, v in ps.items()})
+    eng = DataParallelEngine(mod, fm.DistributedOptimizer(rule), overlap=False, sync_params=False,
+                             algo="oneshot" if not big else "twoshot")
+    st = R.setup(fm.DistributedOptimizer(rule), ps)
+    for step in range(3):
+        g = torch.Generator().manual_seed(100 * step + r)
+        gs = {k: torch.randn(v.shape, generator=g).to(dev) for k, v in ps.items()}
+        for k, p in mod.items():
+            p.grad.copy_(gs[k])
+        eng.step()
+        before = _native.launch_count
+        st, ps = R.update_(st, ps, gs)
+        used = _native.launch_count - before
+        assert used <= 2, f"functional step took {used} launches"
+        assert used == (2 if big else 1), (big, used)
+    torch.cuda.synchronize()
+    for k, p in mod.items():
+        same = torch.equal(p.detach(), ps[k])
+        # one-shot: both paths add the W gradients in rank order => identical bits. Two launches
+        # (in-switch or slice-owner sums) round like the engine's owner path only on average.
+        assert same or (big and torch.allclose(p.detach(), ps[k], rtol=1e-5, atol=1e-6)), (k, big, (p.detach() - ps[k]).abs().max())
+    c = F.checksum(torch.cat([v.reshape(-1) for v in ps.values()])).reshape(1)
+    lo, hi = c.clone(), c.clone()
+    fm.allreduce_(lo, "min"); fm.allreduce_(hi, "max")
+    assert int(lo) == int(hi), "functional-path replicas drifted"
+    # the non-mutating form leaves its inputs alone and agrees with the mutating one
+    keep = {k: v.clone() for k, v in ps.items()}
+    gs = {k: torch.ones_like(v) for k, v in ps.items()}
+    st2, ps2 = R.update(st, ps, gs)
+    assert all(torch.equal(ps[k], keep[k]) for k in ps) and not torch.equal(ps2["p0"], ps["p0"])
+    eng.close()
+
+
+if dw.native:
+    functional_vs_engine(R.Adam(1e-3), big=False)
+    functional_vs_engine(R.Momentum(0.01, 0.9), big=False)
+    functional_vs_engine(R.Adam(1e-3), big=True)
+    # allreduce_gradients on a tree: gather + all-reduce in one launch, scatter in a second
+    from fluxmpi_b200 import _native as _nv
+    tree = {"a": torch.full((1000, 33), float(r + 1), device=dev), "b": (torch.full((7,), float(r), device=dev),)}
+    before = _nv.launch_count
+    fm.allreduce_gradients(tree)
+    assert _nv.launch_count - before == 2, _nv.launch_count - before
+    assert torch.equal(tree["a"], torch.full((1000, 33), w * (w + 1) / 2, device=dev))
+    assert torch.equal(tree["b"][0], torch.full((7,), w * (w - 1) / 2, device=dev))
+
 run("twoshot", True, 0.05)
 run("twoshot", False, 1000.0)
 run("twoshot", True, 0.05, graph=True)

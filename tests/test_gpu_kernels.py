@@ -465,6 +465,106 @@ def test_multi_tensor_step(rule, dtype):
         assert torch.allclose(ps[i].float().cpu(), want, rtol=tol, atol=tol), (i, rule)
 
 
+def _tree_tables(ew, w, shapes, dtype, rule, gen, misalign=False):
+    """Per virtual rank: parameter / gradient / moment leaves and the device table of
+    csrc/kernels/tree_step.cu ([p | g | m | v | numel | flat offset])."""
+    h = F.hyper_for(rule)
+    need_m, need_v = F.rule_needs(h)
+    es = 4 if dtype == torch.float32 else 2
+    p0 = [torch.randn(s, generator=gen).to(dtype) for s in shapes]
+    ranks = []
+    for r in range(w):
+        def leaf(src, dt=dtype):
+            if not misalign:
+                return src.to(DEV).to(dt).clone()
+            buf = torch.zeros(src.numel() + 1, dtype=dt, device=DEV)     # element offset 1: not 16-byte aligned
+            buf[1:].copy_(src.reshape(-1))
+            return buf[1:].view(src.shape)
+        ps = [leaf(p) for p in p0]
+        gs = [torch.empty_like(p) for p in ps]
+        ms = [torch.zeros(s, device=DEV) for s in shapes] if need_m else None
+        vs = [torch.zeros(s, device=DEV) for s in shapes] if need_v else None
+        ranks.append((ps, gs, ms, vs))
+    offs, total = [], 0
+    for s_ in p0:
+        offs.append(total)
+        total += (s_.numel() * es + 15) // 16 * 16
+    n = len(shapes)
+    tabs = []
+    for ps, gs, ms, vs in ranks:
+        z = [0] * n
+        rows = [[t.data_ptr() for t in ps], [t.data_ptr() for t in gs], [t.data_ptr() for t in ms] if ms else z,
+                [t.data_ptr() for t in vs] if vs else z, [t.numel() for t in ps], offs]
+        tabs.append(torch.tensor([x for row in rows for x in row], dtype=torch.int64, device=DEV))
+    return h, p0, ranks, tabs, offs, total
+
+
+@pytest.mark.parametrize("w", [2, 3, 8])
+@pytest.mark.parametrize("rule", [R.Descent(0.1), R.Nesterov(0.05, 0.9), R.Adam(1e-2), R.AdamW(1e-2, (0.9, 0.99), 1e-3)],
+                         ids=["Descent", "Nesterov", "Adam", "AdamW"])
+@pytest.mark.parametrize("dtype,misalign", [(torch.float32, False), (torch.bfloat16, False), (torch.float32, True)])
+def test_tree_step_oneshot_matches_reference(w, rule, dtype, misalign):
+    """One launch for `update!` through a DistributedOptimizer on scattered leaves: push, one
+    barrier, rank-ordered sum, rule applied in place — against the fp32 rule fed the summed
+    gradient; every replica ends with the same bits."""
+    ew = EmulatedWorld(w, DEV, window_mb=1, stage_mb=8)
+    gen = torch.Generator().manual_seed(21)
+    shapes = [(3,), (17, 5), (8192 + 5,), (1, 1), (20000,), (64, 33)]
+    h, p0, ranks, tabs, offs, total = _tree_tables(ew, w, shapes, dtype, rule, gen, misalign)
+    hist = [[] for _ in shapes]
+    for step in range(4):
+        for i, s_ in enumerate(shapes):
+            gsum = None
+            for r in range(w):
+                g = torch.randn(s_, generator=gen).to(dtype)
+                ranks[r][1][i].copy_(g)
+                gsum = g.float() if gsum is None else gsum + g.float()
+            hist[i].append(gsum)
+        ew.tree_step_oneshot(tabs, len(shapes), total, dtype, h, step, ew.ar_off, ew.ar_bytes, blocks=(0, 1, 3, 2)[step])
+    torch.cuda.synchronize()
+    tol = 2e-5 if dtype == torch.float32 else 3e-2
+    for i in range(len(shapes)):
+        p = p0[i].float()
+        st = rule.init(p)
+        for g in hist[i]:
+            st, dx = rule.apply(st, p, g)
+            p = (p - dx).to(dtype).float()
+        for r in range(w):
+            got = ranks[r][0][i]
+            assert torch.allclose(got.float().cpu(), p, rtol=tol, atol=tol), (w, i, r, (got.float().cpu() - p).abs().max())
+            assert torch.equal(got, ranks[0][0][i]), "replicas must be bit-identical"
+
+
+@pytest.mark.parametrize("w", [2, 3, 8])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_tree_allreduce_gathers_and_reduces_in_one_launch(w, dtype):
+    ew = EmulatedWorld(w, DEV, window_mb=4, stage_mb=1)
+    gen = torch.Generator().manual_seed(22)
+    shapes = [(5,), (300, 7), (70001,), (2,), (4096, 16)]
+    h, p0, ranks, tabs, offs, total = _tree_tables(ew, w, shapes, dtype, R.Descent(0.1), gen)
+    off = ew.heap_alloc(total + 64)
+    es = 4 if dtype == torch.float32 else 2
+    for rep in range(3):
+        want = []
+        for i, s_ in enumerate(shapes):
+            gsum = None
+            for r in range(w):
+                g = torch.randn(s_, generator=gen).to(dtype)
+                ranks[r][1][i].copy_(g)
+                gsum = g.double() if gsum is None else gsum + g.double()
+            want.append(gsum)
+        ew.tree_allreduce(tabs, len(shapes), off, total, dtype, _native.SUM, blocks=(0, 2, 5)[rep])
+        torch.cuda.synchronize()
+        tol = 1e-5 if dtype == torch.float32 else 6e-2
+        for r in range(w):
+            arena = ew.window(r, off, total)
+            for i, s_ in enumerate(shapes):
+                n = p0[i].numel()
+                got = arena[offs[i]:offs[i] + n * es].view(dtype).view(s_)
+                assert torch.allclose(got.double().cpu(), want[i], rtol=tol, atol=tol), (w, rep, r, i)
+                assert torch.equal(got, ew.window(0, off, total)[offs[i]:offs[i] + n * es].view(dtype).view(s_))
+
+
 def test_pack_unpack_roundtrip():
     lib = _native.cuda()
     gen = torch.Generator().manual_seed(9)
