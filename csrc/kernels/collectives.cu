@@ -168,6 +168,48 @@ __device__ __forceinline__ void reduce_loop(uint64_t lo, uint64_t hi, uint64_t t
   }
 }
 
+// The same loop with the register budget of the raw vectors (64 registers) spent according to
+// the world size: 8 element groups in flight at W <= 2, 4 at W <= 4, 2 at W <= 8. With few ranks a
+// thread has few loads per element group, and a remote load takes microseconds: without the extra
+// groups in flight a two-rank reduction is latency-bound at ~300 GB/s (measured, 64 CTAs).
+template <typename T, int U, int MAXW, bool kPeerWritten, typename AddrFn, typename StoreFn>
+__device__ __forceinline__ void reduce_loop_n(uint64_t lo, uint64_t hi, uint64_t t0, uint64_t stride,
+                                              int world, int op, AddrFn addr, StoreFn st) {
+  using V = VecOps<T>;
+  for (uint64_t i = lo + t0; i < hi; i += U * stride) {
+    uint4 raw[U][MAXW];
+#pragma unroll
+    for (int k = 0; k < U; ++k)
+      if (i + k * stride < hi) {
+#pragma unroll
+        for (int r = 0; r < MAXW; ++r)
+          if (r < world)
+            raw[k][r] = kPeerWritten ? ld_volatile(addr(r, i + k * stride)) : ld_stream(addr(r, i + k * stride));
+      }
+#pragma unroll
+    for (int k = 0; k < U; ++k)
+      if (i + k * stride < hi) {
+        typename V::Acc acc[V::kN], b[V::kN];
+        V::unpack(raw[k][0], acc);
+#pragma unroll
+        for (int r = 1; r < MAXW; ++r)
+          if (r < world) {
+            V::unpack(raw[k][r], b);
+#pragma unroll
+            for (int e = 0; e < V::kN; ++e) acc[e] = op_apply(acc[e], b[e], op);
+          }
+        st(i + k * stride, V::pack(acc));
+      }
+  }
+}
+template <typename T, bool kPeerWritten, typename AddrFn, typename StoreFn>
+__device__ __forceinline__ void reduce_loop_w(uint64_t lo, uint64_t hi, uint64_t t0, uint64_t stride,
+                                              int world, int op, AddrFn addr, StoreFn st) {
+  if (world <= 2) reduce_loop_n<T, 8, 2, kPeerWritten>(lo, hi, t0, stride, world, op, addr, st);
+  else if (world <= 4) reduce_loop_n<T, 4, 4, kPeerWritten>(lo, hi, t0, stride, world, op, addr, st);
+  else reduce_loop_n<T, 2, 8, kPeerWritten>(lo, hi, t0, stride, world, op, addr, st);
+}
+
 template <typename Fn>
 __device__ __forceinline__ void store_to_ranks(const fmpi_devcomm& c, int dest_root, int skip, Fn ptr_of,
                                                uint4 v) {
@@ -243,7 +285,7 @@ twoshot_symm_kernel(fmpi_devcomm c, uint64_t off, uint64_t nvec, int op, int des
   const uint64_t lo = min(per * x.rank, nvec), hi = min(lo + per, nvec);
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
   const uint64_t t0 = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
-  reduce_loop<T, 2, false>(
+  reduce_loop_w<T, false>(
       lo, hi, t0, stride, c.world, op, [&](int r, uint64_t j) { return byte_ptr(c.data[r], off) + j * 16; },
       [&](uint64_t j, uint4 v) {
         store_to_ranks(c, dest_root, -1, [&](int r) { return byte_ptr(c.data[r], off) + j * 16; }, v);
@@ -307,7 +349,7 @@ twoshot_stage_kernel(fmpi_devcomm c, PtrTable in, PtrTable out, uint64_t nvec, i
     const uint8_t* base = byte_ptr(c.data[x.rank], stage_off);
     const int me = x.rank;
     const bool mine_too = dest_root < 0 || dest_root == me;
-    reduce_loop<T, 2, true>(
+    reduce_loop_w<T, true>(
         lo, hi, t0, stride, c.world, op,
         [&](int r, uint64_t j) { return r == me ? src + j * 16 : base + uint64_t(r) * scatter_bytes + (j - lo) * 16; },
         [&](uint64_t j, uint4 v) {
@@ -559,6 +601,7 @@ struct PipeArgs {
   uint64_t nvec, chunk_vec, stage_off;
   int nslots, kind, root, op;   // kind: 0 all-reduce, 1 reduce to root, 2 broadcast from root
   int n_link, n_copy;           // CTAs in the link role; the rest are split over in / out
+  uint64_t* trace;              // diagnostics (FMPI_PIPE_TRACE=1): [3 roles][256 chunks][4] globaltimer stamps
 };
 enum { kPipeIn = 0, kPipeLink = 1, kPipeOut = 2 };
 
@@ -634,6 +677,9 @@ pipe_kernel(fmpi_devcomm c, PipeArgs a) {
       const uint64_t per = ceil_div(cv, uint64_t(W));
       const uint64_t soff = a.stage_off + uint64_t(s) * slot_bytes;
 
+      uint64_t* tr = (a.trace && idx == 0 && threadIdx.x == 0 && k < 256 && arg_index(c) == 0)
+                         ? a.trace + (uint64_t(role) * 256 + k) * 4 : nullptr;
+      if (tr) tr[0] = globaltimer_ns();
       if (role == kPipeIn) {
         if (u > 0) {
           if (a.kind == 2) wait_peers(kPipeOut, s, U - 1, -1, a.root);  // receivers emptied the slot
@@ -642,6 +688,7 @@ pipe_kernel(fmpi_devcomm c, PipeArgs a) {
             if (n_out > 0) wait_local(kPipeOut, s, uint32_t(n_out) * u);
           }
         }
+        if (tr) tr[1] = globaltimer_ns();
         if (a.kind != 2) {
           uint8_t* slot = byte_ptr(c.data[me], soff);
           vec_loop<8>(0, cv, t0, stride, [&](uint64_t j) { return ld_stream(src + (v0 + j) * 16); },
@@ -666,9 +713,12 @@ pipe_kernel(fmpi_devcomm c, PipeArgs a) {
                         [&](uint64_t j, uint4 v) { st_stream(slot + j * 16, v); });
           }
         }
+        if (tr) tr[2] = globaltimer_ns();
         done(kPipeIn, s, uint32_t(n_in) * (u + 1), U);
+        if (tr) tr[3] = globaltimer_ns();
       } else if (role == kPipeLink) {
         wait_peers(kPipeIn, s, U, a.kind == 2 ? a.root : -1, -1);
+        if (tr) tr[1] = globaltimer_ns();
         const uint64_t lo = min(per * me, cv), hi = min(lo + per, cv);
         if (a.kind == 2) {
           const uint8_t* mine = byte_ptr(c.data[me], soff);
@@ -694,20 +744,25 @@ pipe_kernel(fmpi_devcomm c, PipeArgs a) {
                       });
         } else {
           const int dest_root = a.kind == 1 ? a.root : -1;
-          reduce_loop<T, 2, false>(
+          reduce_loop_w<T, false>(
               lo, hi, t0, stride, W, a.op, [&](int r, uint64_t j) { return byte_ptr(c.data[r], soff) + j * 16; },
               [&](uint64_t j, uint4 v) {
                 store_to_ranks(c, dest_root, -1, [&](int r) { return byte_ptr(c.data[r], soff) + j * 16; }, v);
               });
         }
+        if (tr) tr[2] = globaltimer_ns();
         done(kPipeLink, s, uint32_t(a.n_link) * (u + 1), U);
+        if (tr) tr[3] = globaltimer_ns();
       } else {
         if (direct) wait_peers(kPipeIn, s, U, a.root, -1);
         else wait_peers(kPipeLink, s, U, -1, -1);
+        if (tr) tr[1] = globaltimer_ns();
         const uint8_t* slot = byte_ptr(c.data[me], soff);
         vec_loop<8>(0, cv, t0, stride, [&](uint64_t j) { return ld_volatile(slot + j * 16); },
                     [&](uint64_t j, uint4 v) { st_stream(dst + (v0 + j) * 16, v); });
+        if (tr) tr[2] = globaltimer_ns();
         done(kPipeOut, s, uint32_t(n_out) * (u + 1), U);
+        if (tr) tr[3] = globaltimer_ns();
       }
     }
 
@@ -963,8 +1018,36 @@ bool pipe_wanted(const fmpi_devcomm* c, int algo, uint64_t nbytes, int kind) {
   if (c->world < 2) return false;
   if (algo == FMPI_ALGO_PIPE) return true;
   if (algo != FMPI_ALGO_AUTO) return false;
+  // Opt-in only (FMPI_PIPE_AUTO=1 lets AUTO choose it from min_ar / min_other bytes up). Measured
+  // on 8 B200s (profiles/runs/r2/pipe_trace_*_8.log): per 16 MB chunk the roles work 25 us (in),
+  // 13 us (link, in-switch) and 10 us (out) but each waits 15-50 us for the slowest of the eight
+  // ranks at every hand-over, so a 256 MB all-reduce reaches 367-418 GB/s bus bandwidth where the
+  // single staged kernel reaches ~500 (and the in-place symmetric kernel 811). At 2 GPUs with the
+  // peer-to-peer link phase the three roles share the SMs' load/store bandwidth: 200-300 GB/s
+  // against 320-460 staged. The kernel stays as a selectable algorithm (FMPI_ALGO_PIPE).
   const PipeCfg& cfg = pipe_cfg();
+  static const bool auto_on = [] { const char* v = getenv("FMPI_PIPE_AUTO"); return v && *v && *v != '0'; }();
+  if (!auto_on) return false;
+  if (!(c->mc_data && !c->emulate && c->world >= cfg.nvls_min_world)) return false;
   return nbytes >= (kind == 0 ? cfg.min_ar : cfg.min_other);
+}
+
+// Diagnostics: with FMPI_PIPE_TRACE=1 the first CTA of every role stamps globaltimer per chunk
+// (start, after its wait, after its copy / link work, after its hand-over) into this buffer;
+// fmpi_pipe_trace_read copies the stamps of the LAST pipelined call to the host.
+constexpr size_t kPipeTraceWords = 3 * 256 * 4;
+uint64_t* pipe_trace_buffer(bool clear = true) {
+  static uint64_t* buf = [] {
+    const char* v = getenv("FMPI_PIPE_TRACE");
+    uint64_t* p = nullptr;
+    if (v && *v && *v != '0') cudaMalloc(&p, kPipeTraceWords * sizeof(uint64_t));
+    return p;
+  }();
+  if (buf && clear) {
+    cudaDeviceSynchronize();
+    cudaMemset(buf, 0, kPipeTraceWords * sizeof(uint64_t));
+  }
+  return buf;
 }
 
 // kind: 0 all-reduce, 1 reduce, 2 broadcast. The region [stage_off, stage_off + stage_bytes) is
@@ -996,6 +1079,10 @@ int pipe_impl(const fmpi_devcomm* c, const void* const* in, void* const* out, ui
   } else {
     a.n_link = nvls ? cfg.link_nvls : cfg.link_p2p;
     total = a.n_link + (nvls ? cfg.copy_nvls : cfg.copy_p2p);
+    if (!nvls && c->world <= 2 && kind != 2) {   // two ranks: the link role carries half the bytes itself
+      a.n_link = cfg.link_p2p + cfg.copy_p2p / 2;
+      total = cfg.link_p2p + cfg.copy_p2p;
+    }
   }
   int cap = 144;                                   // co-resident: one CTA per SM, a few SMs spare
   if (c->emulate) cap = 128 / c->world;
@@ -1005,6 +1092,7 @@ int pipe_impl(const fmpi_devcomm* c, const void* const* in, void* const* out, ui
   if (total - a.n_link < 2) total = a.n_link + 2;
   a.n_copy = total - a.n_link;
   int threads = (l && l->threads > 0 && l->threads <= 512) ? (l->threads + 31) / 32 * 32 : 512;
+  a.trace = pipe_trace_buffer();
   int rc = 0;
   if (nvls) {
     FMPI_DISPATCH_NVLS(kind == 2 ? FMPI_F32 : dtype,
@@ -1025,7 +1113,7 @@ int bcast_mode(const fmpi_devcomm* c, int algo, uint64_t nbytes, bool symm = fal
   if (algo == FMPI_ALGO_TWOSHOT) return c->world > 2 ? 1 : 0;
   // large symmetric messages: every rank fetches its slice from the root and re-emits it, so
   // all W links send at once (the root's multicast alone tops out near 350-390 GB/s)
-  if (symm && c->world > 2 && nbytes >= (4u << 20)) return 3;
+  if (symm && c->world > 2 && nbytes >= (8u << 20)) return 3;
   if (mc && c->world > 2) return 2;
   return (nbytes >= (1u << 20) && c->world > 2) ? 1 : 0;
 }
@@ -1117,6 +1205,14 @@ int fmpi_bcast_any(const fmpi_devcomm* c, void* const* buf, uint64_t nbytes, int
                        *c, t, n, root, stage_off, half, mode);
   }
   return rc;
+}
+
+int fmpi_pipe_trace_read(uint64_t* host_out, size_t nwords) {
+  uint64_t* b = pipe_trace_buffer(false);
+  if (!b) return set_error("FMPI_PIPE_TRACE is not set");
+  if (nwords > kPipeTraceWords) nwords = kPipeTraceWords;
+  if (check_cuda(cudaDeviceSynchronize(), "sync")) return 1;
+  return check_cuda(cudaMemcpy(host_out, b, nwords * sizeof(uint64_t), cudaMemcpyDeviceToHost), "trace copy");
 }
 
 int fmpi_flush_l2(void* buf, uint64_t nbytes, fmpi_stream st) {

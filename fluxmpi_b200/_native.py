@@ -212,6 +212,7 @@ def cuda():
         lib.fmpi_bcast_any.argtypes = [dc, vp, u64, i32, u64, u64, lp, vp]
         lib.fmpi_reduce_any.argtypes = [dc, vp, vp, u64, i32, i32, i32, u64, u64, lp, vp]
         lib.fmpi_barrier_dev.argtypes = [dc, vp]
+        lib.fmpi_pipe_trace_read.argtypes = [vp, C.c_size_t]
         lib.fmpi_fused_step.argtypes = [dc, u64, i32, u64, i32, vp, vp, vp, u64, u64,
                                         C.POINTER(Hyper), vp, lp, vp]
         lib.fmpi_fused_step_oneshot.argtypes = [dc, u64, u64, i32, vp, vp, vp, u64, u64,

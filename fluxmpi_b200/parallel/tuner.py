@@ -24,11 +24,11 @@ from .._native import Launch
 _ALGO = {"auto": _native.ALGO_AUTO, "oneshot": _native.ALGO_ONESHOT, "twoshot": _native.ALGO_TWOSHOT,
          "nvls": _native.ALGO_NVLS, "pipe": _native.ALGO_PIPE}
 
-# Sizes from which the library's own choice (FMPI_ALGO_AUTO) is a kernel family the round-1 grids
-# never measured: the chunk-pipelined staged kernels for ordinary buffers and the pull + re-emit
-# broadcast on symmetric memory (csrc/kernels/collectives.cu: pipe_cfg(), bcast_mode()). A table
-# without "pipe" rows must not shadow them; a re-measured table (rows with "algo": "pipe") may.
-_AUTO_FROM = {"allreduce_any": 48 << 20, "reduce_any": 8 << 20, "bcast_any": 8 << 20, "bcast_symm": 4 << 20}
+# Sizes from which the library's own choice (FMPI_ALGO_AUTO) is a kernel the round-1 grids never
+# measured: the pull + re-emit broadcast on symmetric memory (csrc/kernels/collectives.cu,
+# bcast_mode(): 268 / 371 / 470 / 491 GB/s at 16 MB / 64 MB / 256 MB / 1 GB on 8 GPUs against
+# 134-394 for the tuned root-multicast rows). A table without "pipe" rows must not shadow it.
+_AUTO_FROM = {"bcast_symm": 8 << 20}
 
 
 class Tuner:

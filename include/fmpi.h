@@ -262,6 +262,11 @@ int fmpi_reduce_any(const fmpi_devcomm* c, const void* const* in, void* const* o
                     uint64_t count, int dtype, int op, int root, uint64_t stage_off,
                     uint64_t stage_bytes, const fmpi_launch* l, fmpi_stream st);
 int fmpi_barrier_dev(const fmpi_devcomm* c, fmpi_stream st);
+/* Diagnostics of the chunk-pipelined kernels: with FMPI_PIPE_TRACE=1 in the environment the first
+ * CTA of each role (in, link, out) stamps %globaltimer per chunk — start, after its wait, after
+ * its work, after its hand-over — and this call copies the [3][256][4] stamps of the last
+ * pipelined collective to the host (synchronises the device). */
+int fmpi_pipe_trace_read(uint64_t* host_out, size_t nwords);
 
 /* ---- fused gradient allreduce (+) optimiser step (the headline kernel).
  * Gradients (dtype gdt) at g_off and parameters (dtype pdt) at p_off live in the symmetric

@@ -105,9 +105,13 @@ def functional_vs_engine(rule, big: bool):
     torch.cuda.synchronize()
     for k, p in mod.items():
         same = torch.equal(p.detach(), ps[k])
-        # one-shot: both paths add the W gradients in rank order => identical bits. Two launches
+        # one-shot: both paths add the W gradients in rank order => identical bits (Adam's bias
+        # correction is computed on the device by the engine and on the host by the tree kernel:
+        # powf may differ in the last place, so Adam is compared to rounding). Two launches
         # (in-switch or slice-owner sums) round like the engine's owner path only on average.
-        assert same or (big and torch.allclose(p.detach(), ps[k], rtol=1e-5, atol=1e-6)), (k, big, (p.detach() - ps[k]).abs().max())
+        exact = not big and isinstance(rule, R.Momentum)
+        assert same or (not exact and torch.allclose(p.detach(), ps[k], rtol=1e-5, atol=1e-6)), \
+            (k, big, (p.detach() - ps[k]).abs().max())
     c = F.checksum(torch.cat([v.reshape(-1) for v in ps.values()])).reshape(1)
     lo, hi = c.clone(), c.clone()
     fm.allreduce_(lo, "min"); fm.allreduce_(hi, "max")

@@ -257,20 +257,23 @@ def test_tuner_lookup(tmp_path, monkeypatch):
         {"bytes": 64 << 20, "algo": "nvls", "blocks": 148, "threads": 512}]}}))
     t = Tuner(4, True, str(f))
     assert t.choice("allreduce_any", 2 << 20) == ("twoshot", 32, 256)       # nearest on a log scale
-    assert t.choice("allreduce_any", 40 << 20) == ("nvls", 148, 512)
-    # from 48 MB up a table without "pipe" rows leaves the choice to the library (chunk pipeline)
-    assert t.choice("allreduce_any", 100 << 20) is None
+    assert t.choice("allreduce_any", 100 << 20) == ("nvls", 148, 512)
+    # large in-place broadcasts are left to the library (pull + re-emit) unless the table was re-measured
     f2 = tmp_path / "tuned2.json"
-    f2.write_text(json.dumps({"4": {"allreduce_any": [
-        {"bytes": 256 << 20, "algo": "pipe", "blocks": 64, "threads": 512}]}}))
-    assert Tuner(4, True, str(f2)).choice("allreduce_any", 200 << 20) == ("pipe", 64, 512)
+    f2.write_text(json.dumps({"4": {"bcast_symm": [
+        {"bytes": 64 << 20, "algo": "nvls", "blocks": 16, "threads": 512}]}}))
+    assert Tuner(4, True, str(f2)).choice("bcast_symm", 6 << 20) is not None
+    assert Tuner(4, True, str(f2)).choice("bcast_symm", 64 << 20) is None
+    f2.write_text(json.dumps({"4": {"bcast_symm": [
+        {"bytes": 64 << 20, "algo": "pipe", "blocks": 64, "threads": 512}]}}))
+    assert Tuner(4, True, str(f2)).choice("bcast_symm", 64 << 20) == ("pipe", 64, 512)
     assert t.choice("allreduce_any", 1000) is None                          # below the measured range
     assert t.choice("bcast_any", 1 << 20) is None                           # no table for this op
     ref, obj = t.launch("allreduce_any", 3 << 20)
     assert (obj.blocks, obj.threads, obj.algo) == (32, 256, 2)
     assert t.launch("allreduce_any", 3 << 20)[1] is obj                     # cached per size bucket
     no_mc = Tuner(4, False, str(f))
-    assert no_mc.choice("allreduce_any", 40 << 20) == ("twoshot", 32, 256)  # nvls rows dropped
+    assert no_mc.choice("allreduce_any", 100 << 20) == ("twoshot", 32, 256)  # nvls rows dropped
     assert Tuner(8, True, str(f)).choice("allreduce_any", 1 << 20) is None
     monkeypatch.setenv("FMPI_NO_TUNE", "1")
     assert Tuner(4, True, str(f)).choice("allreduce_any", 2 << 20) is None
