@@ -261,8 +261,9 @@ def test_tuner_lookup(tmp_path, monkeypatch):
     # large in-place broadcasts are left to the library (pull + re-emit) unless the table was re-measured
     f2 = tmp_path / "tuned2.json"
     f2.write_text(json.dumps({"4": {"bcast_symm": [
+        {"bytes": 4 << 20, "algo": "nvls", "blocks": 8, "threads": 512},
         {"bytes": 64 << 20, "algo": "nvls", "blocks": 16, "threads": 512}]}}))
-    assert Tuner(4, True, str(f2)).choice("bcast_symm", 6 << 20) is not None
+    assert Tuner(4, True, str(f2)).choice("bcast_symm", 6 << 20) == ("nvls", 8, 512)
     assert Tuner(4, True, str(f2)).choice("bcast_symm", 64 << 20) is None
     f2.write_text(json.dumps({"4": {"bcast_symm": [
         {"bytes": 64 << 20, "algo": "pipe", "blocks": 64, "threads": 512}]}}))
