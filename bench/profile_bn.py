@@ -61,11 +61,16 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--out", default="")
+    ap.add_argument("--only", default="", help="hw,C pairs to keep, e.g. 28,512;56,64 (ncu runs: keep it short)")
+    ap.add_argument("--no-pool", action="store_true")
     a = ap.parse_args()
+    keep = {tuple(int(v) for v in item.split(",")) for item in a.only.split(";") if item}
     dev = torch.device("cuda", 0)
     peak = peak_gbs()
     rows = []
     for hw, C, relu, res in SHAPES:
+        if keep and (hw, C) not in keep:
+            continue
         shape = (a.batch, C, hw, hw)
         x = torch.randn(shape, device=dev).bfloat16().contiguous(memory_format=torch.channels_last).requires_grad_(True)
         r = torch.randn(shape, device=dev).bfloat16().contiguous(memory_format=torch.channels_last).requires_grad_(True) if res else None
@@ -86,7 +91,8 @@ def main():
         # passes over the activation tensor: fwd = stats read + apply (read x [+res], write y);
         # bwd = reduce (dy, x [, y]) + apply (dy, x [, y] read; dx [, dres] written)
         p_f = 1 + 2 + (1 if res else 0)
-        p_b = (2 + (1 if relu else 0)) * 2 + 1 + (1 if (res and relu) else 0)
+        need_y = relu and res               # the ReLU mask is recomputed from x unless a residual went in
+        p_b = (2 + (1 if need_y else 0)) * 2 + 1 + (1 if (res and relu) else 0)
         rows.append({"hw": hw, "C": C, "relu": relu, "residual": res, "tensor_mb": round(nbytes / 2 ** 20, 1),
                      "fwd_us": round(t_f, 1), "fwd_passes": p_f, "fwd_gbs": round(p_f * nbytes / t_f / 1e3, 1),
                      "fwd_frac_of_measured_hbm": round(p_f * nbytes / t_f / 1e3 / peak, 3),
@@ -95,6 +101,8 @@ def main():
         print(json.dumps(rows[-1]), flush=True)
         del x, r, dy, bn, ys
         torch.cuda.empty_cache()
+    if a.no_pool:
+        return _finish(a, peak, rows)
     # stem max-pool 3x3 / 2 on 112x112x64
     x = torch.randn(a.batch, 64, 112, 112, device=dev).bfloat16().contiguous(memory_format=torch.channels_last).requires_grad_(True)
     mp = FusedMaxPool2d(3, 2, 1)
@@ -112,6 +120,10 @@ def main():
                  "fwd_gbs": round((nin + nout + nout // 2) / t_f / 1e3, 1),
                  "bwd_us": round(t_b, 1), "bwd_gbs": round((nin + nout + nout // 2) / t_b / 1e3, 1)})
     print(json.dumps(rows[-1]), flush=True)
+    _finish(a, peak, rows)
+
+
+def _finish(a, peak, rows):
     if a.out:
         Path(a.out).parent.mkdir(parents=True, exist_ok=True)
         Path(a.out).write_text(json.dumps({"hbm_gbs_measured": peak, "batch": a.batch, "dtype": "bf16",

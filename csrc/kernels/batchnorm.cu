@@ -18,8 +18,17 @@
 //
 //   forward : stats -> finalize (mean, invstd, scale, shift, running stats) -> apply
 //             y = relu?(x * scale + shift (+ residual))
-//   backward: reduce (sum dz, sum dz*xhat; dz = dy * (y > 0) when ReLU is fused) -> finalize
+//   backward: reduce (sum dz, sum dz*xhat; dz = dy * mask when ReLU is fused) -> finalize
 //             (d_beta, d_gamma, coefficients) -> apply dx = a * (dz - b1 - xhat * b2), d_res = dz
+//
+// Statistics are accumulated around a per-channel pivot (the channel's value in row 0):
+// sum(x - pivot) and sum((x - pivot)^2) in fp32 per thread, folded in double. With the plain
+// E[x^2] - mean^2 form a channel whose |mean| is far above its standard deviation (post-ReLU
+// activations, an un-normalised first layer) loses the variance to cancellation.
+//
+// The ReLU mask of a layer WITHOUT a residual input is recomputed in the backward kernels from
+// x (x * scale + shift > 0, the fp32 expression the forward pass rounded) instead of being read
+// from the forward output y: two of the seven passes over the activations of such a layer go away.
 #include "common.cuh"
 
 namespace fmpi {
@@ -97,18 +106,24 @@ __device__ __forceinline__ void lanes_reduce(float* v, float* sm, int tx, int ty
 // ---------------------------------------------------------------------------- forward
 template <typename T>
 __global__ void __launch_bounds__(kBNThreads)
-bn_stats_kernel(const T* __restrict__ x, uint64_t M, int C, int tx, uint64_t rows_per_cta, float* __restrict__ partial) {
+bn_stats_kernel(const T* __restrict__ x, uint64_t M, int C, int tx, uint64_t rows_per_cta, float* __restrict__ partial,
+                float* __restrict__ pivot_out) {
   using V = VecOps<T>;
   constexpr int N = V::kN;
   extern __shared__ float sm[];
   const int ty = blockDim.x / tx;
   const BNIdx i = bn_idx<N>(M, C, tx, rows_per_cta);
-  float acc[2 * N];
+  float acc[2 * N], piv[N];
 #pragma unroll
   for (int k = 0; k < 2 * N; ++k) acc[k] = 0.f;
   if (i.act) {
     const uint8_t* base = reinterpret_cast<const uint8_t*>(x) + uint64_t(i.vc) * 16;
     const uint64_t rb = uint64_t(C) * sizeof(T);
+    V::unpack(*reinterpret_cast<const uint4*>(base), piv);       // row 0: the same pivot in every CTA
+    if (blockIdx.x == 0 && i.ry == 0) {
+#pragma unroll
+      for (int k = 0; k < N; ++k) pivot_out[i.vc * N + k] = piv[k];
+    }
     for (uint64_t r = i.r0 + i.ry; r < i.r1; r += 4ull * ty) {
       uint4 raw[4];
 #pragma unroll
@@ -121,8 +136,9 @@ bn_stats_kernel(const T* __restrict__ x, uint64_t M, int C, int tx, uint64_t row
           V::unpack(raw[u], e);
 #pragma unroll
           for (int k = 0; k < N; ++k) {
-            acc[k] += e[k];
-            acc[N + k] += e[k] * e[k];
+            const float d = e[k] - piv[k];
+            acc[k] += d;
+            acc[N + k] += d * d;
           }
         }
     }
@@ -168,7 +184,7 @@ __device__ __forceinline__ void fold_partials(const float* __restrict__ partial,
 }
 
 __global__ void __launch_bounds__(kFoldC * kFoldG)
-bn_fwd_finalize_kernel(const float* __restrict__ partial, unsigned gx, uint64_t M, int C,
+bn_fwd_finalize_kernel(const float* __restrict__ partial, const float* __restrict__ pivot, unsigned gx, uint64_t M, int C,
                        const float* __restrict__ gamma, const float* __restrict__ beta,
                        float* running_mean, float* running_var, float momentum, float eps,
                        float* save_mean, float* save_invstd, float* scale, float* shift) {
@@ -176,8 +192,9 @@ bn_fwd_finalize_kernel(const float* __restrict__ partial, unsigned gx, uint64_t 
   double s, q;
   fold_partials(partial, gx, C, c, s, q);
   if (c >= C || threadIdx.y != 0) return;
-  const double mean = s / double(M);
-  double var = q / double(M) - mean * mean;
+  const double dm = s / double(M);                   // mean of (x - pivot)
+  const double mean = double(pivot[c]) + dm;
+  double var = q / double(M) - dm * dm;              // shift-invariant: no cancellation against the mean
   if (var < 0.0) var = 0.0;
   const float invstd = float(1.0 / sqrt(var + double(eps)));
   save_mean[c] = float(mean);
@@ -236,11 +253,14 @@ bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res, T* __restric
 }
 
 // ---------------------------------------------------------------------------- backward
-template <typename T, bool kRelu>
+// kMask: 0 no ReLU, 1 mask from the forward output y, 2 mask recomputed from x (no residual)
+template <typename T, int kMask>
 __global__ void __launch_bounds__(kBNThreads)
 bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x, uint64_t M, int C,
                      int tx, uint64_t rows_per_cta, const float* __restrict__ mean,
-                     const float* __restrict__ invstd, float* __restrict__ partial) {
+                     const float* __restrict__ invstd, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, float* __restrict__ partial) {
+  constexpr bool kRelu = kMask == 1;
   using V = VecOps<T>;
   constexpr int N = V::kN;
   extern __shared__ float sm[];
@@ -250,9 +270,16 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T*
 #pragma unroll
   for (int k = 0; k < 2 * N; ++k) acc[k] = 0.f;
   if (i.act) {
-    float mu[N], is[N];
+    float mu[N], is[N], sc[N], sh[N];
     load_consts<N>(mean, i.vc * N, mu);
     load_consts<N>(invstd, i.vc * N, is);
+    if (kMask == 2) {
+#pragma unroll
+      for (int k = 0; k < N; ++k) {
+        sc[k] = (gamma ? gamma[i.vc * N + k] : 1.f) * is[k];
+        sh[k] = (beta ? beta[i.vc * N + k] : 0.f) - mu[k] * sc[k];
+      }
+    }
     const uint64_t rb = uint64_t(C) * sizeof(T);
     const uint64_t col = uint64_t(i.vc) * 16;
     const uint8_t* db = reinterpret_cast<const uint8_t*>(dy) + col;
@@ -277,7 +304,8 @@ bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T*
           if (kRelu) V::unpack(yr[u], ye);
 #pragma unroll
           for (int k = 0; k < N; ++k) {
-            const float dz = (kRelu && !(ye[k] > 0.f)) ? 0.f : d[k];
+            const bool off = kMask == 1 ? !(ye[k] > 0.f) : kMask == 2 ? !(xe[k] * sc[k] + sh[k] > 0.f) : false;
+            const float dz = off ? 0.f : d[k];
             acc[k] += dz;
             acc[N + k] += dz * (xe[k] - mu[k]) * is[k];
           }
@@ -310,12 +338,13 @@ bn_bwd_finalize_kernel(const float* __restrict__ partial, unsigned gx, uint64_t 
   b2[c] = float(s2 / double(M));
 }
 
-template <typename T, bool kRelu, bool kRes>
+template <typename T, int kMask, bool kRes>
 __global__ void __launch_bounds__(kBNThreads)
 bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x, T* __restrict__ dx,
                     T* __restrict__ dres, uint64_t M, int C, int tx, uint64_t rows_per_cta,
                     const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ a,
-                    const float* __restrict__ b1, const float* __restrict__ b2) {
+                    const float* __restrict__ b1, const float* __restrict__ b2, const float* __restrict__ beta) {
+  constexpr bool kRelu = kMask == 1;
   using V = VecOps<T>;
   constexpr int N = V::kN;
   const int ty = blockDim.x / tx;
@@ -327,6 +356,11 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* 
   load_consts<N>(a, i.vc * N, ca);
   load_consts<N>(b1, i.vc * N, c1);
   load_consts<N>(b2, i.vc * N, c2);
+  float sh[N];
+  if (kMask == 2) {     // a = gamma * invstd is the forward scale; shift = beta - mean * scale
+#pragma unroll
+    for (int k = 0; k < N; ++k) sh[k] = (beta ? beta[i.vc * N + k] : 0.f) - mu[k] * ca[k];
+  }
   const uint64_t rb = uint64_t(C) * sizeof(T);
   const uint64_t col = uint64_t(i.vc) * 16;
   const uint8_t* db = reinterpret_cast<const uint8_t*>(dy) + col;
@@ -354,7 +388,8 @@ bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* 
         if (kRelu) V::unpack(yr[u], ye);
 #pragma unroll
         for (int k = 0; k < N; ++k) {
-          const float dz = (kRelu && !(ye[k] > 0.f)) ? 0.f : d[k];
+          const bool off = kMask == 1 ? !(ye[k] > 0.f) : kMask == 2 ? !(xe[k] * ca[k] + sh[k] > 0.f) : false;
+          const float dz = off ? 0.f : d[k];
           d[k] = dz;
           const float xh = (xe[k] - mu[k]) * is[k];
           g[k] = ca[k] * (dz - c1[k] - xh * c2[k]);
@@ -373,8 +408,8 @@ using fmpi_host::set_error;
 
 namespace {
 
-// scratch (floats): partial[kBNMaxGx][2][C] | scale | shift | a | b1 | b2
-size_t bn_scratch_floats(int C) { return size_t(kBNMaxGx) * 2 * C + 5 * size_t(C); }
+// scratch (floats): partial[kBNMaxGx][2][C] | scale | shift | a | b1 | b2 | pivot
+size_t bn_scratch_floats(int C) { return size_t(kBNMaxGx) * 2 * C + 6 * size_t(C); }
 
 template <typename T>
 int bn_forward_t(const void* x, const void* res, void* y, uint64_t M, int C, const float* gamma, const float* beta,
@@ -387,8 +422,9 @@ int bn_forward_t(const void* x, const void* res, void* y, uint64_t M, int C, con
   float* shift = scale + C;
   const dim3 grid(g.gx, g.gy);
   const size_t smem = size_t(kBNThreads) * 2 * N * sizeof(float);
-  bn_stats_kernel<T><<<grid, kBNThreads, smem, st>>>(static_cast<const T*>(x), M, C, g.tx, g.rows_per_cta, partial);
-  bn_fwd_finalize_kernel<<<(C + kFoldC - 1) / kFoldC, dim3(kFoldC, kFoldG), 0, st>>>(partial, g.gx, M, C, gamma, beta, rmean, rvar, momentum,
+  float* pivot = scale + 5 * size_t(C);
+  bn_stats_kernel<T><<<grid, kBNThreads, smem, st>>>(static_cast<const T*>(x), M, C, g.tx, g.rows_per_cta, partial, pivot);
+  bn_fwd_finalize_kernel<<<(C + kFoldC - 1) / kFoldC, dim3(kFoldC, kFoldG), 0, st>>>(partial, pivot, g.gx, M, C, gamma, beta, rmean, rvar, momentum,
                                                           eps, save_mean, save_invstd, scale, shift);
   const T* xp = static_cast<const T*>(x);
   const T* rp = static_cast<const T*>(res);
@@ -424,8 +460,8 @@ int bn_apply_t(const void* x, const void* res, void* y, uint64_t M, int C, const
 
 template <typename T>
 int bn_backward_t(const void* dy, const void* y, const void* x, void* dx, void* dres, uint64_t M, int C,
-                  const float* gamma, const float* mean, const float* invstd, float* dgamma, float* dbeta, int relu,
-                  float* scratch, cudaStream_t st) {
+                  const float* gamma, const float* beta, const float* mean, const float* invstd, float* dgamma,
+                  float* dbeta, int relu, float* scratch, cudaStream_t st) {
   constexpr int N = VecOps<T>::kN;
   const BNGeom g = bn_geom(M, C / N);
   float* partial = scratch;
@@ -439,16 +475,20 @@ int bn_backward_t(const void* dy, const void* y, const void* x, void* dx, void* 
   const T* xp = static_cast<const T*>(x);
   T* op = static_cast<T*>(dx);
   T* rp = static_cast<T*>(dres);
-  if (relu) bn_bwd_reduce_kernel<T, true><<<grid, kBNThreads, smem, st>>>(dp, yp, xp, M, C, g.tx, g.rows_per_cta, mean, invstd, partial);
-  else bn_bwd_reduce_kernel<T, false><<<grid, kBNThreads, smem, st>>>(dp, yp, xp, M, C, g.tx, g.rows_per_cta, mean, invstd, partial);
+  // mask: 0 none; 1 from y (a residual was added before the ReLU, or the caller passed y);
+  //       2 recomputed from x (ReLU straight after the affine transform, y == NULL)
+  const int mask = !relu ? 0 : (yp ? 1 : 2);
+#define FMPI_BN_REDUCE(MASK) \
+  bn_bwd_reduce_kernel<T, MASK><<<grid, kBNThreads, smem, st>>>(dp, yp, xp, M, C, g.tx, g.rows_per_cta, mean, invstd, gamma, beta, partial)
+  if (mask == 0) FMPI_BN_REDUCE(0); else if (mask == 1) FMPI_BN_REDUCE(1); else FMPI_BN_REDUCE(2);
+#undef FMPI_BN_REDUCE
   bn_bwd_finalize_kernel<<<(C + kFoldC - 1) / kFoldC, dim3(kFoldC, kFoldG), 0, st>>>(partial, g.gx, M, C, gamma, invstd, dgamma, dbeta, a, b1, b2);
-  if (relu) {
-    if (dres) bn_bwd_apply_kernel<T, true, true><<<grid, kBNThreads, 0, st>>>(dp, yp, xp, op, rp, M, C, g.tx, g.rows_per_cta, mean, invstd, a, b1, b2);
-    else bn_bwd_apply_kernel<T, true, false><<<grid, kBNThreads, 0, st>>>(dp, yp, xp, op, rp, M, C, g.tx, g.rows_per_cta, mean, invstd, a, b1, b2);
-  } else {
-    if (dres) bn_bwd_apply_kernel<T, false, true><<<grid, kBNThreads, 0, st>>>(dp, yp, xp, op, rp, M, C, g.tx, g.rows_per_cta, mean, invstd, a, b1, b2);
-    else bn_bwd_apply_kernel<T, false, false><<<grid, kBNThreads, 0, st>>>(dp, yp, xp, op, rp, M, C, g.tx, g.rows_per_cta, mean, invstd, a, b1, b2);
-  }
+#define FMPI_BN_APPLY(MASK, RES) \
+  bn_bwd_apply_kernel<T, MASK, RES><<<grid, kBNThreads, 0, st>>>(dp, yp, xp, op, rp, M, C, g.tx, g.rows_per_cta, mean, invstd, a, b1, b2, beta)
+  if (mask == 0) { if (dres) FMPI_BN_APPLY(0, true); else FMPI_BN_APPLY(0, false); }
+  else if (mask == 1) { if (dres) FMPI_BN_APPLY(1, true); else FMPI_BN_APPLY(1, false); }
+  else { if (dres) FMPI_BN_APPLY(2, true); else FMPI_BN_APPLY(2, false); }
+#undef FMPI_BN_APPLY
   return check_cuda(cudaGetLastError(), "bn_backward launch");
 }
 
@@ -492,17 +532,18 @@ int fmpi_bn_apply(const void* x, const void* res, void* y, uint64_t M, int C, in
 }
 
 int fmpi_bn_backward(const void* dy, const void* y, const void* x, void* dx, void* dres, uint64_t M, int C, int dtype,
-                     const float* gamma, const float* save_mean, const float* save_invstd, float* dgamma,
-                     float* dbeta, int relu, void* scratch, fmpi_stream st) {
+                     const float* gamma, const float* beta, const float* save_mean, const float* save_invstd,
+                     float* dgamma, float* dbeta, int relu, void* scratch, fmpi_stream st) {
   if (bn_check(M, C, dtype, dy, dx)) return 1;
-  if (relu && !y) return set_error("batch norm backward: the fused ReLU needs the forward output");
+  if (relu && !y && dres)
+    return set_error("batch norm backward: with a residual input the ReLU mask needs the forward output y");
   if (!scratch) return set_error("batch norm: null scratch");
   cudaStream_t s = static_cast<cudaStream_t>(st);
   float* sc = static_cast<float*>(scratch);
   switch (dtype) {
-    case FMPI_F32: return bn_backward_t<float>(dy, y, x, dx, dres, M, C, gamma, save_mean, save_invstd, dgamma, dbeta, relu, sc, s);
-    case FMPI_BF16: return bn_backward_t<__nv_bfloat16>(dy, y, x, dx, dres, M, C, gamma, save_mean, save_invstd, dgamma, dbeta, relu, sc, s);
-    default: return bn_backward_t<__half>(dy, y, x, dx, dres, M, C, gamma, save_mean, save_invstd, dgamma, dbeta, relu, sc, s);
+    case FMPI_F32: return bn_backward_t<float>(dy, y, x, dx, dres, M, C, gamma, beta, save_mean, save_invstd, dgamma, dbeta, relu, sc, s);
+    case FMPI_BF16: return bn_backward_t<__nv_bfloat16>(dy, y, x, dx, dres, M, C, gamma, beta, save_mean, save_invstd, dgamma, dbeta, relu, sc, s);
+    default: return bn_backward_t<__half>(dy, y, x, dx, dres, M, C, gamma, beta, save_mean, save_invstd, dgamma, dbeta, relu, sc, s);
   }
 }
 

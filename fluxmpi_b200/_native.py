@@ -233,7 +233,7 @@ def cuda():
         lib.fmpi_bn_scratch_bytes.restype = C.c_size_t
         lib.fmpi_bn_forward.argtypes = [vp, vp, vp, u64, i32, i32, vp, vp, vp, vp, f32, f32, i32, vp, vp, vp, vp]
         lib.fmpi_bn_apply.argtypes = [vp, vp, vp, u64, i32, i32, vp, vp, i32, vp]
-        lib.fmpi_bn_backward.argtypes = [vp, vp, vp, vp, vp, u64, i32, i32, vp, vp, vp, vp, vp, i32, vp, vp]
+        lib.fmpi_bn_backward.argtypes = [vp, vp, vp, vp, vp, u64, i32, i32, vp, vp, vp, vp, vp, vp, i32, vp, vp]
         lib.fmpi_maxpool_fwd.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]
         lib.fmpi_maxpool_bwd.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]
         lib.fmpi_flush_l2.argtypes = [vp, u64, vp]

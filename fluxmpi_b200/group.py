@@ -16,9 +16,10 @@ What a group owns
     tables that hold only the members' windows (``parallel/device_world.py``). The multicast object
     spans the whole world, so groups smaller than the world use the peer-to-peer kernels.
 
-On one GPU, collectives of different communicators must be ordered (issue them on one stream):
-they share the staging window. A group collective starts and ends with a device barrier among the
-members, so it can follow or precede collectives of any other communicator safely.
+Every group has staging of its own in the members' windows (a non-member can be inside a world
+collective while the members run a group collective), so collectives of different communicators
+are independent of each other; calls on ONE communicator follow the usual rule: the same sequence
+on every member.
 """
 from __future__ import annotations
 

@@ -81,13 +81,14 @@ class _BNActFn(torch.autograd.Function):
         ctx.has_res = residual is not None
         ctx.affine = (weight is not None, bias is not None)
         ctx.wdtype = weight.dtype if weight is not None else None
-        ctx.save_for_backward(x, y if relu else None, w, mean, invstd)
+        # the ReLU mask is recomputed from x in backward unless a residual went into the ReLU
+        ctx.save_for_backward(x, y if (relu and residual is not None) else None, w, b, mean, invstd)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         lib = _native.cuda()
-        x, y, w, mean, invstd = ctx.saved_tensors
+        x, y, w, b, mean, invstd = ctx.saved_tensors
         N, C, H, W = x.shape
         M = N * H * W
         if not dy.is_contiguous(memory_format=torch.channels_last):
@@ -99,8 +100,8 @@ class _BNActFn(torch.autograd.Function):
         _native.cuda_check(lib.fmpi_bn_backward(
             dy.data_ptr(), y.data_ptr() if y is not None else None, x.data_ptr(), dx.data_ptr(),
             dres.data_ptr() if dres is not None else None, M, C, _DT[x.dtype],
-            w.data_ptr() if w is not None else None, mean.data_ptr(), invstd.data_ptr(),
-            dgamma.data_ptr(), dbeta.data_ptr(), int(ctx.relu), _scratch_for(x.device, C).data_ptr(),
+            w.data_ptr() if w is not None else None, b.data_ptr() if b is not None else None,
+            mean.data_ptr(), invstd.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), int(ctx.relu), _scratch_for(x.device, C).data_ptr(),
             _stream()), "bn_backward")
         _native.count_launch(3)
         if ctx.has_res and not ctx.relu:

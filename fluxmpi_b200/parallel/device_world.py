@@ -105,6 +105,7 @@ class DeviceWorld(_Base):
     AR_STAGE_MB = (int(os.environ.get("FMPI_AR_STAGE_MB", 160)), int(os.environ.get("FMPI_AR_ASYNC_STAGE_MB", 64)))
     BCAST_STAGE_MB = (int(os.environ.get("FMPI_BCAST_STAGE_MB", 96)), int(os.environ.get("FMPI_BCAST_ASYNC_STAGE_MB", 32)))
     TREE_SLOT_MB = 4
+    GROUP_AR_MB, GROUP_BC_MB = 16, 8
     MAX_COMMS = 8            # signal-pad sets: 0 = the world, 1.. = rank groups (fm.Group)
 
     def __init__(self, rank: int, world: int, device: int, job: str):
@@ -298,6 +299,12 @@ class DeviceWorld(_Base):
         # that kernel family because peers write into them without a handshake
         self.tree_region = (off, 2 * self.world * self.TREE_SLOT_MB * MB)
         off += self.tree_region[1]
+        # every rank group gets staging of its own: a non-member may be in a world collective while
+        # the members are in a group collective, and neither may push into the other's slots
+        self.group_regions = {}
+        for gid in range(1, self.MAX_COMMS):
+            self.group_regions[gid] = ((off, self.GROUP_AR_MB * MB), (off + self.GROUP_AR_MB * MB, self.GROUP_BC_MB * MB))
+            off += (self.GROUP_AR_MB + self.GROUP_BC_MB) * MB
         self._window_bytes = off
         self.ar_off, self.ar_bytes = self.ar_regions[0]
         self.bc_off, self.bc_bytes = self.bc_regions[0]
@@ -526,9 +533,9 @@ class DeviceWorld(_Base):
     # ------------------------------------------------------------------ rank groups
     def _group_call(self, kind: str, t: torch.Tensor, op: int, root: int, group, channel: int = 0, stream=None):
         """A collective over a rank subset (fm.Group). Native worlds: the staged kernels on the
-        group's own communicator (its signal pads, the members' windows only), bracketed by two
-        device barriers among the members so that it can follow or precede collectives of any
-        other communicator on this GPU's staging window. Otherwise: through the group's host world."""
+        group's own communicator — its signal pads, the members' windows only, and a staging region
+        of its own, so it is independent of whatever the world or another group is doing on the same
+        GPUs. Otherwise: through the group's host world."""
         if group.size == 1 or t.numel() == 0:
             return t
         if not self.native:
@@ -546,14 +553,15 @@ class DeviceWorld(_Base):
         st = (torch.cuda.current_stream() if stream is None else stream).cuda_stream
         w, copy = self._work_tensor(t)
         nbytes = w.numel() * w.element_size()
-        cuda_check(lib.fmpi_barrier_dev(ref, st), "group barrier")
+        (g_ar_off, g_ar_bytes), (g_bc_off, g_bc_bytes) = self.group_regions[group.id]
+        half = 1 if channel == 1 else 0                 # blocking / non-blocking calls: separate halves
         if kind == "bcast":
-            bc_off, bc_bytes = self.bc_regions[1 if channel == 1 else 0]
+            bc_off, bc_bytes = g_bc_off + half * (g_bc_bytes // 2), g_bc_bytes // 2
             self._in1.value = w.data_ptr()
             rc = lib.fmpi_bcast_any(ref, self._in1_ref, nbytes, root, bc_off, bc_bytes, self._lp_auto, st)
             cuda_check(rc, "group bcast")
         else:
-            ar_off, ar_bytes = self.ar_regions[1 if channel == 1 else 0]
+            ar_off, ar_bytes = g_ar_off + half * (g_ar_bytes // 2), g_ar_bytes // 2
             es, n = w.element_size(), w.numel()
             code = _DT[w.dtype]
             bulk = n if nbytes % 16 == 0 or nbytes <= (200 << 10) else (nbytes // 16 * 16) // es
@@ -569,8 +577,7 @@ class DeviceWorld(_Base):
                                                  ar_bytes, self._lp_auto, st)
                     cuda_check(rc, "group " + kind)
                 off += cnt
-        cuda_check(lib.fmpi_barrier_dev(ref, st), "group barrier")
-        _native.launch_count += 3
+        _native.launch_count += 1
         if copy and (kind == "allreduce" or (kind == "reduce") == (group.rank == root)):
             self._copy_back(t, w)
         return t

@@ -358,7 +358,11 @@ int fmpi_sumsq_noalloc(const void* x, uint64_t count, int dtype, double* out, fm
  *   forward : y = relu?(batchnorm(x) (+ res)); updates running stats; saves mean / invstd
  *   apply   : y = relu?(x * scale + shift (+ res))           (inference, precomputed affine)
  *   backward: dx, dgamma, dbeta (and dres = dy masked by the ReLU when res was given); `y` is
- *             the forward output (needed only when relu != 0).
+ *             the forward output: needed only when relu != 0 AND a residual was added — with
+ *             y == NULL the ReLU mask is recomputed from x, gamma, beta and the saved statistics
+ *             (two fewer passes over the activations).
+ * The statistics are accumulated around a per-channel pivot, so channels whose mean is far from
+ * zero keep their variance (no E[x^2] - mean^2 cancellation).
  * The reference ships no model code; this exists because these ops, not the
  * convolutions, dominate the headline ResNet-50 step on B200 (profiles/README.md §7). */
 size_t fmpi_bn_scratch_bytes(int C);
@@ -369,7 +373,7 @@ int fmpi_bn_forward(const void* x, const void* res, void* y, uint64_t M, int C, 
 int fmpi_bn_apply(const void* x, const void* res, void* y, uint64_t M, int C, int dtype,
                   const float* scale, const float* shift, int relu, fmpi_stream st);
 int fmpi_bn_backward(const void* dy, const void* y, const void* x, void* dx, void* dres, uint64_t M,
-                     int C, int dtype, const float* gamma, const float* save_mean,
+                     int C, int dtype, const float* gamma, const float* beta, const float* save_mean,
                      const float* save_invstd, float* dgamma, float* dbeta, int relu, void* scratch,
                      fmpi_stream st);
 

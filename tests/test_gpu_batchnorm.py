@@ -82,6 +82,68 @@ def test_forward_backward_match_pytorch(shape, dtype, relu, use_res):
         assert ok, worst
 
 
+@pytest.mark.parametrize("ratio", [10.0, 100.0, 1000.0])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("relu", [False, True])
+def test_statistics_survive_a_mean_far_above_the_deviation(ratio, dtype, relu):
+    """|mean| / sigma in {10, 100, 1000} per channel (post-ReLU activations, an un-normalised
+    first layer): E[x^2] - mean^2 in fp32 cancels there; the pivoted sums do not. Compared with a
+    float64 restatement on the values the kernel actually sees (after the 16-bit rounding)."""
+    g = torch.Generator().manual_seed(int(ratio))
+    N, C, H, W = 6, 64, 14, 14
+    sigma = torch.rand(C, generator=g) * 0.5 + 0.25
+    mean = sigma * ratio * torch.where(torch.rand(C, generator=g) < 0.5, -1.0, 1.0)
+    x = torch.randn(N, C, H, W, generator=g) * sigma.view(1, C, 1, 1) + mean.view(1, C, 1, 1)
+    x = x.cuda().to(dtype).contiguous(memory_format=torch.channels_last)
+    w = (torch.rand(C, generator=g) + 0.5).cuda()
+    b = (torch.randn(C, generator=g) * 0.2).cuda()
+    rm, rv = torch.zeros(C).cuda(), torch.ones(C).cuda()
+    xd = x.double().detach().requires_grad_(True)
+    m64 = xd.mean(dim=(0, 2, 3))
+    v64 = xd.var(dim=(0, 2, 3), unbiased=False)
+    y64 = (xd - m64.view(1, C, 1, 1)) / torch.sqrt(v64.view(1, C, 1, 1) + 1e-5) * w.double().view(1, C, 1, 1) + b.double().view(1, C, 1, 1)
+    if relu:
+        y64 = torch.relu(y64)
+    xk = x.clone().requires_grad_(True)
+    y = fused_bn_act(xk, w, b, rm, rv, True, 1.0, 1e-5, relu=relu)       # momentum 1: running = batch statistics
+    # forward: the normalised output is O(1); a lost variance shows up as O(1) errors at once
+    tol = 5e-2 if dtype == torch.bfloat16 else 2e-3 * max(1.0, ratio / 100)
+    assert torch.allclose(y.double(), y64, rtol=tol, atol=tol), float((y.double() - y64).abs().max())
+    assert torch.allclose(rm.double(), m64, rtol=1e-5, atol=1e-5), float((rm.double() - m64).abs().max())
+    n = N * H * W
+    assert torch.allclose(rv.double(), v64 * n / (n - 1), rtol=2e-3), float((rv.double() / (v64 * n / (n - 1)) - 1).abs().max())
+    dy = torch.randn(N, C, H, W, generator=g).cuda().to(dtype).contiguous(memory_format=torch.channels_last)
+    y64.backward(dy.double())
+    y.backward(dy)
+    gtol = 6e-2 if dtype == torch.bfloat16 else 5e-3 * max(1.0, ratio / 100)
+    scale = float(xd.grad.abs().max())
+    bad = (xk.grad.double() - xd.grad).abs() > gtol * scale
+    assert float(bad.double().mean()) <= (2e-3 if relu else 0.0), float((xk.grad.double() - xd.grad).abs().max() / scale)
+
+
+def test_relu_mask_is_recomputed_from_x_without_a_residual():
+    """BN + ReLU without a residual saves no forward output for backward (the mask is
+    x * scale + shift > 0); with a residual it keeps y."""
+    x = torch.randn(4, 32, 8, 8, device="cuda").contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    r = torch.randn(4, 32, 8, 8, device="cuda").contiguous(memory_format=torch.channels_last)
+    bn = FusedBatchNormAct(32, relu=True).cuda()
+    y = bn(x)
+    saved = y.grad_fn.saved_tensors
+    assert not any(t is not None and t.data_ptr() == y.data_ptr() for t in saved)
+    y2 = bn(x, r)
+    assert any(t is not None and t.data_ptr() == y2.data_ptr() for t in y2.grad_fn.saved_tensors)
+    # and the gradient equals the one PyTorch computes from the mask of y
+    ref = torch.nn.BatchNorm2d(32).cuda()
+    ref.load_state_dict(bn.state_dict())
+    xr = x.detach().clone().requires_grad_(True)
+    dy = torch.randn_like(y)
+    bn2 = FusedBatchNormAct(32, relu=True).cuda()
+    bn2.load_state_dict(ref.state_dict())
+    bn2(x).backward(dy)
+    F.relu(ref(xr)).backward(dy)
+    assert torch.allclose(x.grad, xr.grad, rtol=2e-3, atol=2e-4), float((x.grad - xr.grad).abs().max())
+
+
 def test_module_matches_batchnorm2d_train_and_eval():
     torch.manual_seed(0)
     ref = torch.nn.BatchNorm2d(32).cuda()
