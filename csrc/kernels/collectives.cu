@@ -424,7 +424,7 @@ bcast_symm_kernel(fmpi_devcomm c, uint64_t off, uint64_t nvec, int root, int mod
   const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
   const uint64_t t0 = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
   const uint8_t* src = byte_ptr(c.data[x.rank], off);
-  if (mode == 3) {
+  if (mode >= 3) {
     // pull + re-emit: rank q loads slice q from the ROOT's window (the root's link carries the
     // message once, spread over W-1 readers) and stores it to every other rank — through the
     // multicast alias when there is one — so all W links send at once. The root's own slice is
@@ -434,11 +434,11 @@ bcast_symm_kernel(fmpi_devcomm c, uint64_t off, uint64_t nvec, int root, int mod
     const uint64_t lo = min(per * x.rank, nvec), hi = min(lo + per, nvec);
     const uint8_t* rsrc = byte_ptr(c.data[root], off);
     const int me = x.rank;
-    if (c.mc_data && !c.emulate) {
+    if (c.mc_data && !c.emulate && mode == 3) {
       uint8_t* mc = byte_ptr(c.mc_data, off);
       vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_stream(rsrc + j * 16); },
                   [&](uint64_t j, uint4 v) { multimem_st(mc + j * 16, v); });
-    } else {
+    } else {   // mode 4, or no multicast mapping: re-emit with W - 2 peer stores
       vec_loop<4>(lo, hi, t0, stride, [&](uint64_t j) { return ld_stream(rsrc + j * 16); },
                   [&](uint64_t j, uint4 v) {
 #pragma unroll
@@ -1108,6 +1108,7 @@ int pipe_impl(const fmpi_devcomm* c, const void* const* in, void* const* out, ui
 int bcast_mode(const fmpi_devcomm* c, int algo, uint64_t nbytes, bool symm = false) {
   const bool mc = c->mc_data && !c->emulate;
   if (algo == FMPI_ALGO_PIPE) return symm ? 3 : (c->world > 2 ? 1 : 0);
+  if (algo == FMPI_ALGO_PULL_P2P) return symm ? 4 : (c->world > 2 ? 1 : 0);
   if (algo == FMPI_ALGO_NVLS) return mc ? 2 : -1;
   if (algo == FMPI_ALGO_ONESHOT) return 0;
   if (algo == FMPI_ALGO_TWOSHOT) return c->world > 2 ? 1 : 0;
@@ -1163,7 +1164,10 @@ int fmpi_bcast_symm(const fmpi_devcomm* c, uint64_t off, uint64_t nbytes, int ro
   if (nbytes == 0) return 0;
   const int mode = bcast_mode(c, l ? l->algo : FMPI_ALGO_AUTO, nbytes, true);
   if (mode < 0) return set_error("multicast broadcast requested but no multicast mapping");
-  const Shape s = pick_shape(c, l, mode == 3 ? nbytes / c->world : nbytes);
+  Shape s = pick_shape(c, l, mode >= 3 ? nbytes / c->world : nbytes);
+  // pull + multicast re-emit: the switch replicates, 16 CTAs saturate it and more only add
+  // contention (8 GPUs, 1 GB: 513 GB/s with 16 CTAs, 481 with 64, 393 with 148; symm_probe_8.json)
+  if (mode == 3 && c->mc_data && !c->emulate && !(l && l->blocks > 0) && s.blocks > 16) s.blocks = 16;
   return launch_ranked(bcast_symm_kernel, *c, s.blocks, s.threads, static_cast<cudaStream_t>(st),
                        *c, off, nvec, root, mode);
 }

@@ -20,7 +20,7 @@ NUM_CHANNELS = 4
 F32, F64, F16, BF16, I32, I64, U8, I8, I16 = range(9)
 SUM, PROD, MIN, MAX = range(4)
 RULE_DESCENT, RULE_MOMENTUM, RULE_NESTEROV, RULE_ADAM, RULE_ADAMW = range(5)
-ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS, ALGO_PIPE = range(5)
+ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS, ALGO_PIPE, ALGO_PULL_P2P = range(6)
 SYMM_VMM, SYMM_IPC, SYMM_LOCAL = range(3)
 
 OPS = {"sum": SUM, "+": SUM, "add": SUM, "prod": PROD, "*": PROD, "mul": PROD,

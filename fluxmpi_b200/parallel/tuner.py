@@ -22,7 +22,7 @@ from .. import _native
 from .._native import Launch
 
 _ALGO = {"auto": _native.ALGO_AUTO, "oneshot": _native.ALGO_ONESHOT, "twoshot": _native.ALGO_TWOSHOT,
-         "nvls": _native.ALGO_NVLS, "pipe": _native.ALGO_PIPE}
+         "nvls": _native.ALGO_NVLS, "pipe": _native.ALGO_PIPE, "pull_p2p": _native.ALGO_PULL_P2P}
 
 # Sizes from which the library's own choice (FMPI_ALGO_AUTO) is a kernel the round-1 grids never
 # measured: the pull + re-emit broadcast on symmetric memory (csrc/kernels/collectives.cu,

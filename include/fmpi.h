@@ -237,7 +237,8 @@ size_t fmpi_sigpad_bytes(void);
 /* Launch-shape hints; 0 = library default chosen from message size. */
 typedef struct { int32_t blocks; int32_t threads; int32_t algo; } fmpi_launch;
 enum { FMPI_ALGO_AUTO = 0, FMPI_ALGO_ONESHOT = 1, FMPI_ALGO_TWOSHOT = 2, FMPI_ALGO_NVLS = 3,
-       FMPI_ALGO_PIPE = 4 /* chunk-pipelined staging (large ordinary buffers) */ };
+       FMPI_ALGO_PIPE = 4, /* chunk-pipelined staging (ordinary buffers); symmetric bcast: pull + multicast re-emit */
+       FMPI_ALGO_PULL_P2P = 5 /* symmetric bcast: pull the slice from the root, re-emit with peer stores */ };
 
 /* Collectives on buffers that already live in the symmetric window at byte offset `off`
  * (in-place, result in every rank's window for allreduce/bcast, root only for reduce). */

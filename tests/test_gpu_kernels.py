@@ -284,10 +284,14 @@ def test_symmetric_bcast_pull_and_reemit(worlds, w):
             for r in range(w):
                 got[r].fill_(float(r))
             got[root].copy_(src)
-            ew.bcast_symm(off, n * 4, root, algo=_native.ALGO_PIPE)
-            torch.cuda.synchronize()
-            for r in range(w):
-                assert torch.equal(got[r], src), (w, n, root, r)
+            for algo in (_native.ALGO_PIPE, _native.ALGO_PULL_P2P):
+                for r in range(w):
+                    if r != root:
+                        got[r].fill_(float(r))
+                ew.bcast_symm(off, n * 4, root, algo=algo)
+                torch.cuda.synchronize()
+                for r in range(w):
+                    assert torch.equal(got[r], src), (w, n, root, r, algo)
 
 
 # ------------------------------------------------------------------ fused allreduce + optimiser
