@@ -656,8 +656,8 @@ pipe_kernel(fmpi_devcomm c, PipeArgs a) {
     if (threadIdx.x == 0) {
       fence_acq_rel_sys();
       if (atomicAdd(counter(rl, s), 1u) + 1 == total) {
-        fence_acq_rel_sys();
-        for (int r = 0; r < W; ++r) st_release_sys(flag_of(r, rl, s, me), value);
+        fence_acq_rel_sys();   // one fence, then relaxed flag stores: a release store each would
+        for (int r = 0; r < W; ++r) st_relaxed_sys(flag_of(r, rl, s, me), value);   // cost W more MEMBAR.SYS
       }
     }
   };
