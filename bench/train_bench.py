@@ -46,7 +46,9 @@ def build(name, dev):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--model", default="vit_b16", choices=["vit_b16", "gpt2_medium", "mlp"])
-    ap.add_argument("--impl", default="ours", choices=["ours", "ddp"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "functional", "ddp"],
+                    help="ours = DataParallelEngine; functional = the reference's loop shape, "
+                         "update!(state, params, grads) through a DistributedOptimizer on the module's own leaves")
     ap.add_argument("--steps", type=int, default=15)
     ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--batch", type=int, default=0)
@@ -96,6 +98,44 @@ def main():
         extra = {"buckets": len(eng.buckets), "comm": fm.runtime.state().device_world.mode +
                  ("+nvls" if eng.algo == _native.ALGO_NVLS else ""), "cuda_graph": not a.no_graph,
                  "master_weights": eng.master is not None, "params": eng.numel}
+        fin = fm.Finalize
+    elif a.impl == "functional":
+        # /root/reference/README.md:61-67: pullback, then Optimisers.update through the
+        # DistributedOptimizer. Leaves stay where the module put them; on CUDA the whole step after
+        # backward is one launch for trees up to 4 MB (csrc/kernels/tree_step.cu), two beyond.
+        import fluxmpi_b200 as fm
+        from fluxmpi_b200 import _native
+        from fluxmpi_b200 import rules as R
+        fm.Init()
+        dev = fm.current_device()
+        torch.manual_seed(rank)
+        model, mk, loss_fn, b0, unit, per_sample, pdt = build(a.model, dev)
+        batch = a.batch or b0
+        model = fm.synchronize(fm.FluxMPIFluxModel(model), root_rank=0)
+        ps = {k: p.detach() for k, p in model.named_parameters()}
+        st = R.setup(fm.DistributedOptimizer(R.Adam(1e-4)), ps)
+        x, y = mk(batch, torch.Generator().manual_seed(rank))
+        use_ac = pdt == torch.float32 and a.model != "mlp"
+        params = list(model.parameters())
+
+        def step(*i):
+            nonlocal st
+            if params[0].grad is not None:
+                torch._foreach_zero_([p.grad for p in params])      # same gradient storage every step
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=use_ac):
+                l = (loss_fn(model, *i) if len(i) == 2 else loss_fn(model, i[0], None)) / world
+            l.backward()
+            st, _ = R.update_(st, ps, {k: p.grad for k, p in model.named_parameters()})
+            return l
+
+        ins = (x,) if y is None else (x, y)
+        for _ in range(max(a.warmup, 3)):
+            step(*ins)
+        before = _native.launch_count
+        ms = headline.timed(lambda k: [step(*ins) for _ in range(k)], a.steps, fm.barrier, "ours")
+        launches = _native.launch_count - before
+        extra = {"comm": fm.runtime.state().device_world.mode, "cuda_graph": False,
+                 "our_launches_per_step": launches / max(a.steps, 1), "params": sum(p.numel() for p in params)}
         fin = fm.Finalize
     else:
         import torch.distributed as dist

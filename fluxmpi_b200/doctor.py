@@ -71,6 +71,24 @@ def _self_test(rep: Report, what: str, nprocs: int, cpu_only: bool = False, **kw
         os.unlink(script)
 
 
+def _device_selftest(rep: Report, nprocs: int):
+    """fluxmpi_b200.selftest over all GPUs of the box: every kernel family through the live world
+    against float64 host references (what bench.py runs before timing)."""
+    from .launch import launch
+    env = {"PYTHONPATH": str(ROOT) + os.pathsep + os.environ.get("PYTHONPATH", ""), "FMPI_TIMEOUT_S": "60"}
+    code, outs = launch(nprocs, ["fluxmpi_b200.selftest"], module=True, timeout=300, env_extra=env, capture=True)
+    line = next((ln for ln in reversed(outs[0].splitlines()) if ln.startswith("{")), "")
+    try:
+        got = json.loads(line) if line else {}
+    except ValueError:
+        got = {}
+    what = f"device self-test, {nprocs} GPUs"
+    if code == 0 and got.get("ok"):
+        rep.add("ok", what, f"{got.get('cases')} cases, mode {got.get('mode')}{'+multicast' if got.get('multicast') else ''}")
+    else:
+        rep.add("FAIL", what, f"exit code {code}; failed: {got.get('failed')}")
+
+
 def main(argv=None) -> int:
     ap = argparse.ArgumentParser(prog="python -m fluxmpi_b200.doctor")
     ap.add_argument("--json", action="store_true", help="print the report as one JSON object at the end")
@@ -122,6 +140,7 @@ def main(argv=None) -> int:
         if ngpu >= 2:
             os.environ.pop("FMPI_FORCE_FALLBACK", None)
             _self_test(rep, "device world, 2 GPUs", 2)
+            _device_selftest(rep, min(ngpu, 8))
     print("doctor:", "problems found" if rep.failed else "all required checks passed")
     if a.json:
         print(json.dumps({"failed": rep.failed, "checks": rep.rows}))
