@@ -64,6 +64,9 @@ mutable struct FlatEngine{T}
     hyper::Hyper
     bucket::Int                     # elements per bucket (multiple of 64)
     nvls::Bool
+    oneshot::Bool                   # whole model <= 2 MB: push + one barrier + replicated rule
+    stage_off::UInt64               # push slots [2 parities][W][n * sizeof(T)] behind [P | G]
+    stage_bytes::UInt64
 end
 
 params(e::FlatEngine) = e.P
@@ -129,7 +132,10 @@ function FlatEngine(ps::CuVector{T}, rule; average::Bool=false, bucket_mb::Real=
     buf = cld(n * es, 1 << 21) << 21
     no = _segment_counter[]
     _segment_counter[] += 1
-    seg, mcptr = _alloc_segment(w, dev, 2 * buf, no)
+    # a Quick-Start-sized model is latency-bound: one-shot flavour (csrc/kernels/fused_step.cu)
+    oneshot = w.size > 1 && n * es <= parse(Int, get(ENV, "FMPI_FUSED_ONESHOT_KB", "2048")) * 1024
+    stage = oneshot ? 2 * w.size * (cld(n * es, 256) * 256) : 0
+    seg, mcptr = _alloc_segment(w, dev, 2 * buf + stage, no)
     base = (w.device::DeviceWorld).comms[1]
     peers = [ccall(csym(:fmpi_symm_peer_ptr), Ptr{Cvoid}, (Ptr{Cvoid}, Cint), seg, q) for q in 0:(w.size - 1)]
     pad(v) = ntuple(i -> i <= length(v) ? v[i] : C_NULL, FMPI_MAX_RANKS)
@@ -144,7 +150,8 @@ function FlatEngine(ps::CuVector{T}, rule; average::Bool=false, bucket_mb::Real=
     master = T === Float32 ? nothing : CuVector{Float32}(P)
     bucket = max(64, (round(Int, bucket_mb * (1 << 20) / es) ÷ 64) * 64)
     eng = FlatEngine{T}(seg, comm, n, UInt64(0), UInt64(buf), P, G, CUDA.zeros(Float32, n), CUDA.zeros(Float32, n),
-                        master, CUDA.zeros(Int64, 1), _hyper(rule, scale), bucket, mcptr != C_NULL && w.size >= 4)
+                        master, CUDA.zeros(Int64, 1), _hyper(rule, scale), oneshot ? n : bucket,
+                        mcptr != C_NULL && w.size >= 4, oneshot, UInt64(2 * buf), UInt64(stage))
     if w.size > 1                       # replicas start from rank 0's values, in one kernel
         ccheck(ccall(csym(:fmpi_bcast_symm), Cint, (Ptr{DevComm}, UInt64, UInt64, Cint, Ptr{Launch}, Ptr{Cvoid}),
                      Ref(comm), 0, n * es, 0, Ref(AUTO), _stream()), "bcast_symm")
@@ -162,7 +169,18 @@ every rank and `grads(eng)` is cleared. Stream-ordered on the current CUDA.jl st
 function step!(e::FlatEngine{T}) where {T}
     code = dtype_code(T)
     one(x) = x === nothing ? C_NULL : Ref{Ptr{Cvoid}}(Base.unsafe_convert(Ptr{Cvoid}, pointer(x)))
-    la = Ref(Launch(96, 0, e.nvls ? 3 : 2))
+    la = Ref(Launch(0, 0, e.nvls ? 3 : 2))       # 0 CTAs: the library's measured default
+    if e.oneshot
+        ccheck(ccall(csym(:fmpi_fused_step_oneshot), Cint,
+                     (Ptr{DevComm}, UInt64, UInt64, Cint, Ptr{Ptr{Cvoid}}, Ptr{Ptr{Cvoid}}, Ptr{Ptr{Cvoid}},
+                      UInt64, UInt64, Ptr{Hyper}, Ptr{Ptr{Cvoid}}, UInt64, UInt64, Ptr{Launch}, Ptr{Cvoid}),
+                     Ref(e.comm), e.g_off, e.p_off, code, one(e.m), one(e.v), one(e.master),
+                     0, e.n, Ref(e.hyper), one(e.step), e.stage_off, e.stage_bytes, Ref(AUTO), _stream()),
+               "fused_step_oneshot")
+        ccheck(ccall(csym(:fmpi_step_advance), Cint, (Ptr{Cvoid}, Ptr{Cvoid}),
+                     Base.unsafe_convert(Ptr{Cvoid}, pointer(e.step)), _stream()), "step_advance")
+        return e
+    end
     lo = 0
     while lo < e.n
         hi = min(lo + e.bucket, e.n)
