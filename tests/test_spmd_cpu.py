@@ -127,3 +127,9 @@ def test_rank_groups_run_different_collectives_concurrently(spmd):
     argument of /root/reference/src/mpi_extensions.jl:97,119,141)."""
     outs = spmd("groups.py", 4)
     assert all(f"RANK_OK {r}" in o for r, o in enumerate(outs))
+
+
+@pytest.mark.parametrize("w", [1, 3])
+def test_group_argument_checks_and_selftest_skip(spmd, w):
+    outs = spmd("extras.py", w)
+    assert all(f"RANK_OK {r}" in o for r, o in enumerate(outs))
