@@ -133,3 +133,9 @@ def test_rank_groups_run_different_collectives_concurrently(spmd):
 def test_group_argument_checks_and_selftest_skip(spmd, w):
     outs = spmd("extras.py", w)
     assert all(f"RANK_OK {r}" in o for r, o in enumerate(outs))
+
+
+def test_randomised_groups_and_world_interleaved(spmd):
+    """tests/spmd/stress_groups.py: three overlapping groups and the world taking turns."""
+    outs = spmd("stress_groups.py", 4, timeout=600, args=("150",))
+    assert all(f"RANK_OK {r}" in o for r, o in enumerate(outs))
