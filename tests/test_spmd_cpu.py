@@ -105,8 +105,8 @@ def test_examples_run_on_cpu(tmp_path):
     assert code == 0 and "HostDataParallelEngine" in outs[0], outs[0][-3000:]
     code, outs = launch(2, [ex, "--epochs", "150", "--checkpoint", ck], timeout=240, env_extra=env, capture=True)
     assert code == 0 and "resumed at epoch 100" in outs[0], outs[0][-3000:]
-    for name in ("quickstart_mlp.py", "flux_style_module.py"):
-        code, outs = launch(2, [str(ROOT / "examples" / name)], timeout=240, env_extra=env, capture=True)
+    for name, n in (("quickstart_mlp.py", 2), ("flux_style_module.py", 2), ("rank_groups.py", 4)):
+        code, outs = launch(n, [str(ROOT / "examples" / name)], timeout=240, env_extra=env, capture=True)
         assert code == 0, (name, outs[0][-3000:])
 
 
