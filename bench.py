@@ -304,8 +304,14 @@ def run_ours(a):
 
     selftest = collectives = None
     if world > 1 and not a.no_extras:
-        selftest = fm.selftest.run()                 # every kernel family through the live world
-        collectives = collectives_probe(rank, world, dev)
+        try:
+            selftest = fm.selftest.run()             # every kernel family through the live world
+        except Exception as e:                       # noqa: BLE001  (reported, never hidden)
+            selftest = {"ok": False, "cases": 0, "failed": [f"{type(e).__name__}: {str(e)[:200]}"]}
+        try:
+            collectives = collectives_probe(rank, world, dev)
+        except Exception as e:                       # noqa: BLE001
+            collectives = {"error": f"{type(e).__name__}: {str(e)[:200]}"}
 
     torch.manual_seed(rank)
     model = make_model(a.model, fused_bn=not a.no_fused_bn).to(dev).to(memory_format=torch.channels_last)
